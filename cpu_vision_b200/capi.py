@@ -1,0 +1,290 @@
+"""ctypes binding of the C-ABI (include/b200_detection_ops.h) on torch tensors.
+
+This is the same boundary a non-Python host would bind; the
+parity tests and bench.py go through it so that what is measured is the C-ABI
+library and not the PyTorch dispatcher.  Device entry points take CUDA tensors
+and launch on torch's current stream; `*_host` entry points take CPU tensors
+(pinned for full PCIe rate) and return after the results are back on the host.
+"""
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+F32, F16, BF16, F64 = 0, 1, 2, 3
+NCHW, NHWC = 0, 1
+BNMS_AUTO, BNMS_TRICK, BNMS_VANILLA = -1, 0, 1
+
+_DT = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16, torch.float64: F64}
+_P, _I, _L, _D, _S = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_size_t
+
+SYMBOLS = [
+    "b200det_version", "b200det_last_error", "b200det_roi_align_forward", "b200det_roi_align_backward",
+    "b200det_fpn_level_map", "b200det_msroi_align_forward", "b200det_msroi_align_backward",
+    "b200det_nms_workspace_bytes", "b200det_nms", "b200det_batched_nms", "b200det_roi_align_forward_host",
+    "b200det_roi_align_backward_host", "b200det_nms_host", "b200det_batched_nms_host", "b200det_host_release",
+]
+
+_declared = False
+
+
+def lib():
+    global _declared
+    l = _lib.capi()
+    if not _declared:
+        l.b200det_version.restype = _I
+        l.b200det_last_error.restype = C.c_char_p
+        l.b200det_roi_align_forward.argtypes = [_P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I, _I, _P]
+        l.b200det_roi_align_backward.argtypes = [_P, _P, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I, _I, _I, _P]
+        l.b200det_fpn_level_map.argtypes = [_P, _I, _L, _I, _I, _I, _I, _D, _P, _P]
+        l.b200det_msroi_align_forward.argtypes = [_P, _P, _P, _P, _I, _I, _P, _P, _I, _P, _I, _I, _L, _L, _L, _L, _L,
+                                                  _I, _I, _I, _I, _I, _I, _D, _P]
+        l.b200det_msroi_align_backward.argtypes = [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _L, _L,
+                                                   _I, _I, _I, _P]
+        l.b200det_nms_workspace_bytes.argtypes = [_L]
+        l.b200det_nms_workspace_bytes.restype = _S
+        l.b200det_nms.argtypes = [_P, _P, _I, _L, _D, _P, _P, _P, _S, _P]
+        l.b200det_batched_nms.argtypes = [_P, _P, _P, _I, _L, _D, _I, _P, _P, _P, _S, _P]
+        l.b200det_roi_align_forward_host.argtypes = [_P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I, _I, _I]
+        l.b200det_roi_align_backward_host.argtypes = [_P, _P, _L, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I,
+                                                      _I, _I]
+        l.b200det_nms_host.argtypes = [_P, _P, _I, _L, _D, _P, _P, _I]
+        l.b200det_batched_nms_host.argtypes = [_P, _P, _P, _I, _L, _D, _I, _P, _P, _I]
+        l.b200det_host_release.restype = None
+        _declared = True
+    return l
+
+
+class B200DetError(RuntimeError):
+    pass
+
+
+def _check(rc, who):
+    if rc != 0:
+        raise B200DetError(f"{who} failed ({rc}): {lib().b200det_last_error().decode()}")
+
+
+def _dt(t):
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {t.dtype}") from None
+
+
+def _layout_of(t):
+    """(layout, dense tensor) for a logically [N,C,H,W] tensor."""
+    if t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last) and not t.is_contiguous():
+        return NHWC, t
+    return NCHW, t.contiguous()
+
+
+def _stream(t):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _arith(rois, feat_dtype):
+    return rois.to(torch.float64 if feat_dtype == torch.float64 else torch.float32).contiguous()
+
+
+def _empty_like_layout(shape, like, layout):
+    mf = torch.channels_last if layout == NHWC else torch.contiguous_format
+    return torch.empty(shape, dtype=like.dtype, device=like.device, memory_format=mf)
+
+
+def _strides(t):
+    return (_L * 4)(*t.stride())
+
+
+# --------------------------------------------------------------------------- device entry points
+def roi_align_forward(x, rois, pooled_h, pooled_w, spatial_scale=1.0, sampling_ratio=-1, aligned=False,
+                      out_layout=None):
+    assert x.is_cuda and rois.is_cuda
+    layout, x = _layout_of(x)
+    out_layout = layout if out_layout is None else out_layout
+    r = _arith(rois, x.dtype)
+    N, Cc, H, W = x.shape
+    K = r.shape[0]
+    out = _empty_like_layout((K, Cc, pooled_h, pooled_w), x, out_layout)
+    with torch.cuda.device(x.device):
+        _check(lib().b200det_roi_align_forward(x.data_ptr(), layout, r.data_ptr(), out.data_ptr(), out_layout, _dt(x),
+                                               N, Cc, H, W, K, pooled_h, pooled_w, float(spatial_scale),
+                                               int(sampling_ratio), int(bool(aligned)), _stream(x)),
+               "b200det_roi_align_forward")
+    return out
+
+
+def roi_align_backward(grad, rois, spatial_scale, pooled_h, pooled_w, N, Cc, H, W, sampling_ratio, aligned,
+                       layout=NCHW, out=None, zero_init=True):
+    assert grad.is_cuda and rois.is_cuda
+    r = _arith(rois, grad.dtype)
+    gi = out if out is not None else _empty_like_layout((N, Cc, H, W), grad, layout)
+    with torch.cuda.device(grad.device):
+        _check(lib().b200det_roi_align_backward(grad.data_ptr(), _strides(grad), r.data_ptr(), gi.data_ptr(), layout,
+                                                _dt(grad), N, Cc, H, W, r.shape[0], pooled_h, pooled_w,
+                                                float(spatial_scale), int(sampling_ratio), int(bool(aligned)),
+                                                int(bool(zero_init)), _stream(grad)),
+               "b200det_roi_align_backward")
+    return gi
+
+
+def fpn_level_map(rois, k_min, k_max, canonical_scale=224, canonical_level=4, eps=1e-6):
+    r = rois.to(torch.float32).contiguous()
+    lv = torch.empty(r.shape[0], dtype=torch.int32, device=r.device)
+    with torch.cuda.device(r.device):
+        _check(lib().b200det_fpn_level_map(r.data_ptr(), F32, r.shape[0], k_min, k_max, canonical_scale,
+                                           canonical_level, float(eps), lv.data_ptr(), _stream(r)),
+               "b200det_fpn_level_map")
+    return lv
+
+
+def _level_arrays(feats: Sequence[torch.Tensor], scales):
+    L = len(feats)
+    return ((_P * L)(*[f.data_ptr() for f in feats]), (_L * L)(*[f.shape[2] for f in feats]),
+            (_L * L)(*[f.shape[3] for f in feats]), (_D * L)(*[float(s) for s in scales]))
+
+
+def msroi_align_forward(feats: List[torch.Tensor], rois, scales, pooled_h, pooled_w, sampling_ratio, aligned=False,
+                        k_min=2, k_max=5, canonical_scale=224, canonical_level=4, eps=1e-6,
+                        levels: Optional[torch.Tensor] = None, out=None):
+    """Returns (output [K,C,PH,PW], levels int32 [K])."""
+    layout, f0 = _layout_of(feats[0])
+    mf = torch.channels_last if layout == NHWC else torch.contiguous_format
+    feats = [f.contiguous(memory_format=mf) for f in feats]
+    r = _arith(rois, f0.dtype)
+    N, Cc = f0.shape[:2]
+    K = r.shape[0]
+    if out is None:
+        out = _empty_like_layout((K, Cc, pooled_h, pooled_w), f0, layout)
+    given = levels is not None
+    if not given:
+        levels = torch.empty(K, dtype=torch.int32, device=f0.device)
+    ptrs, hs, ws, sc = _level_arrays(feats, scales)
+    with torch.cuda.device(f0.device):
+        _check(lib().b200det_msroi_align_forward(ptrs, hs, ws, sc, len(feats), layout, r.data_ptr(), levels.data_ptr(),
+                                                 int(given), out.data_ptr(), layout, _dt(f0), N, Cc, K, pooled_h,
+                                                 pooled_w, int(sampling_ratio), int(bool(aligned)), k_min, k_max,
+                                                 canonical_scale, canonical_level, float(eps), _stream(f0)),
+               "b200det_msroi_align_forward")
+    return out, levels
+
+
+def msroi_align_backward(grad, rois, levels, scales, shapes, pooled_h, pooled_w, sampling_ratio, aligned=False,
+                         layout=NCHW, outs=None, zero_init=True):
+    """shapes: [(N,C,H,W)] per level -> list of gradients in `layout`."""
+    r = _arith(rois, grad.dtype)
+    if outs is None:
+        outs = [_empty_like_layout(tuple(s), grad, layout) for s in shapes]
+    ptrs, hs, ws, sc = _level_arrays(outs, scales)
+    N, Cc = shapes[0][:2]
+    with torch.cuda.device(grad.device):
+        _check(lib().b200det_msroi_align_backward(grad.data_ptr(), _strides(grad), r.data_ptr(), levels.data_ptr(),
+                                                  ptrs, hs, ws, sc, len(outs), layout, _dt(grad), N, Cc, r.shape[0],
+                                                  pooled_h, pooled_w, int(sampling_ratio), int(bool(aligned)),
+                                                  int(bool(zero_init)), _stream(grad)),
+               "b200det_msroi_align_backward")
+    return outs
+
+
+class NmsWorkspace:
+    """Reusable device scratch + output buffers for N boxes (no allocation per call)."""
+
+    def __init__(self, n, device):
+        self.n = n
+        self.bytes = lib().b200det_nms_workspace_bytes(n)
+        self.ws = torch.empty(self.bytes, dtype=torch.uint8, device=device)
+        self.keep = torch.empty(n + 1, dtype=torch.int64, device=device)
+
+
+def nms(boxes, scores, iou_threshold, workspace: Optional[NmsWorkspace] = None, sync=True):
+    """Returns kept indices (sync=True) or (keep_buffer, count_tensor) still on the device."""
+    boxes = boxes.contiguous()
+    scores = scores.to(boxes.dtype).contiguous()
+    n = boxes.shape[0]
+    w = workspace if workspace is not None and workspace.n >= n else NmsWorkspace(n, boxes.device)
+    cnt = w.keep[w.n:]
+    with torch.cuda.device(boxes.device):
+        _check(lib().b200det_nms(boxes.data_ptr(), scores.data_ptr(), _dt(boxes), n, float(iou_threshold),
+                                 w.keep.data_ptr(), cnt.data_ptr(), w.ws.data_ptr(), w.bytes, _stream(boxes)),
+               "b200det_nms")
+    if not sync:
+        return w.keep, cnt
+    return w.keep[: int(cnt.item())].clone()
+
+
+def batched_nms(boxes, scores, idxs, iou_threshold, mode=BNMS_AUTO, workspace: Optional[NmsWorkspace] = None,
+                sync=True):
+    boxes = boxes.contiguous()
+    scores = scores.to(boxes.dtype).contiguous()
+    idxs = idxs.to(torch.int64).contiguous()
+    n = boxes.shape[0]
+    w = workspace if workspace is not None and workspace.n >= n else NmsWorkspace(n, boxes.device)
+    cnt = w.keep[w.n:]
+    with torch.cuda.device(boxes.device):
+        _check(lib().b200det_batched_nms(boxes.data_ptr(), scores.data_ptr(), idxs.data_ptr(), _dt(boxes), n,
+                                         float(iou_threshold), int(mode), w.keep.data_ptr(), cnt.data_ptr(),
+                                         w.ws.data_ptr(), w.bytes, _stream(boxes)),
+               "b200det_batched_nms")
+    if not sync:
+        return w.keep, cnt
+    return w.keep[: int(cnt.item())].clone()
+
+
+# --------------------------------------------------------------------------- host-buffer entry points
+def roi_align_forward_host(x, rois, pooled_h, pooled_w, spatial_scale=1.0, sampling_ratio=-1, aligned=False,
+                           device=0, out=None):
+    assert not x.is_cuda and not rois.is_cuda
+    layout, x = _layout_of(x)
+    r = _arith(rois, x.dtype)
+    N, Cc, H, W = x.shape
+    if out is None:
+        out = _empty_like_layout((r.shape[0], Cc, pooled_h, pooled_w), x, layout)
+    _check(lib().b200det_roi_align_forward_host(x.data_ptr(), layout, r.data_ptr(), out.data_ptr(), layout, _dt(x), N,
+                                                Cc, H, W, r.shape[0], pooled_h, pooled_w, float(spatial_scale),
+                                                int(sampling_ratio), int(bool(aligned)), int(device)),
+           "b200det_roi_align_forward_host")
+    return out
+
+
+def roi_align_backward_host(grad, rois, spatial_scale, pooled_h, pooled_w, N, Cc, H, W, sampling_ratio, aligned,
+                            layout=NCHW, device=0, out=None):
+    assert not grad.is_cuda
+    r = _arith(rois, grad.dtype)
+    gi = out if out is not None else _empty_like_layout((N, Cc, H, W), grad, layout)
+    span = 1 + sum((s - 1) * st for s, st in zip(grad.shape, grad.stride())) if grad.numel() else 0
+    _check(lib().b200det_roi_align_backward_host(grad.data_ptr(), _strides(grad), span, r.data_ptr(), gi.data_ptr(),
+                                                 layout, _dt(grad), N, Cc, H, W, r.shape[0], pooled_h, pooled_w,
+                                                 float(spatial_scale), int(sampling_ratio), int(bool(aligned)),
+                                                 int(device)),
+           "b200det_roi_align_backward_host")
+    return gi
+
+
+def nms_host(boxes, scores, iou_threshold, device=0):
+    boxes = boxes.contiguous()
+    scores = scores.to(boxes.dtype).contiguous()
+    n = boxes.shape[0]
+    keep = torch.empty(max(n, 1), dtype=torch.int64)
+    cnt = C.c_int64(0)
+    _check(lib().b200det_nms_host(boxes.data_ptr(), scores.data_ptr(), _dt(boxes), n, float(iou_threshold),
+                                  keep.data_ptr(), C.addressof(cnt), int(device)), "b200det_nms_host")
+    return keep[: cnt.value]
+
+
+def batched_nms_host(boxes, scores, idxs, iou_threshold, mode=BNMS_AUTO, device=0, keep=None):
+    boxes = boxes.contiguous()
+    scores = scores.to(boxes.dtype).contiguous()
+    idxs = idxs.to(torch.int64).contiguous()
+    n = boxes.shape[0]
+    if keep is None:
+        keep = torch.empty(max(n, 1), dtype=torch.int64)
+    cnt = C.c_int64(0)
+    _check(lib().b200det_batched_nms_host(boxes.data_ptr(), scores.data_ptr(), idxs.data_ptr(), _dt(boxes), n,
+                                          float(iou_threshold), int(mode), keep.data_ptr(), C.addressof(cnt),
+                                          int(device)), "b200det_batched_nms_host")
+    return keep[: cnt.value]
+
+
+def host_release():
+    lib().b200det_host_release()

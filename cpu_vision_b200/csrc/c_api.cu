@@ -1,0 +1,233 @@
+// c_api.cu -- extern "C" entry points declared in include/b200_detection_ops.h.
+// Argument validation, layout bookkeeping and kernel selection live here; the
+// kernels are in roi_align_fast.cu / roi_align_generic.cu / nms_sm100.cu.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200det {
+
+static thread_local char g_err[512] = "";
+
+void set_last_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+size_t dtype_size(int dtype) {
+  switch (dtype) {
+    case B200DET_F32: return 4;
+    case B200DET_F16: return 2;
+    case B200DET_BF16: return 2;
+    case B200DET_F64: return 8;
+  }
+  return 0;
+}
+
+static int check_common(const char* who, int dtype, int layout_a, int layout_b, int64_t N,
+                        int64_t C, int64_t K, int64_t PH, int64_t PW) {
+  if (dtype_size(dtype) == 0) return fail(B200DET_ENOSUP, "%s: unknown dtype %d", who, dtype);
+  if ((layout_a != B200DET_NCHW && layout_a != B200DET_NHWC) ||
+      (layout_b != B200DET_NCHW && layout_b != B200DET_NHWC))
+    return fail(B200DET_EINVAL, "%s: unknown layout", who);
+  if (N < 0 || C < 0 || K < 0 || PH < 0 || PW < 0)
+    return fail(B200DET_EINVAL, "%s: negative size", who);
+  if (PH > 1 << 20 || PW > 1 << 20 || C > 1 << 24)
+    return fail(B200DET_EINVAL, "%s: size out of range", who);
+  return 0;
+}
+
+static int fill_levels(const char* who, LevelArgs& lv, const void* const* feats,
+                       const int64_t* heights, const int64_t* widths, const double* scales,
+                       int num_levels, int layout, int64_t N, int64_t C) {
+  if (num_levels < 1 || num_levels > B200DET_MAX_LEVELS)
+    return fail(B200DET_EINVAL, "%s: num_levels=%d outside [1,%d]", who, num_levels, B200DET_MAX_LEVELS);
+  lv.num_levels = num_levels;
+  lv.layout = layout;
+  lv.batch = N;
+  lv.channels = C;
+  for (int l = 0; l < num_levels; ++l) {
+    if (heights[l] < 0 || widths[l] < 0 || heights[l] > INT32_MAX || widths[l] > INT32_MAX)
+      return fail(B200DET_EINVAL, "%s: bad size of level %d", who, l);
+    if (!feats[l] && N * C * heights[l] * widths[l] != 0)
+      return fail(B200DET_EINVAL, "%s: null feature pointer for level %d", who, l);
+    lv.ptr[l] = const_cast<void*>(feats[l]);
+    lv.height[l] = heights[l];
+    lv.width[l] = widths[l];
+    lv.scale[l] = scales[l];
+  }
+  return 0;
+}
+
+static int forward_impl(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
+                        void* output, int out_layout, int64_t K, int64_t PH, int64_t PW, int sr,
+                        int aligned, cudaStream_t st) {
+  if (K * lv.channels * PH * PW == 0) return 0;
+  if (!rois || !output) return fail(B200DET_EINVAL, "roi_align forward: null pointer");
+  int taken = 0;
+  int rc = roi_align_fwd_fast(lv, dtype, rois, levels, output, out_layout, K, (int)PH, (int)PW, sr,
+                              aligned != 0, st, &taken);
+  if (rc != 0 || taken) return rc;
+  return roi_align_fwd_generic(lv, dtype, rois, levels, output, out_layout, K, (int)PH, (int)PW, sr,
+                               aligned != 0, st);
+}
+
+static int backward_impl(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
+                         const void* rois, const int32_t* levels, int64_t K, int64_t PH, int64_t PW,
+                         int sr, int aligned, int zero_init, cudaStream_t st) {
+  if (zero_init) {
+    for (int l = 0; l < lv.num_levels; ++l) {
+      const size_t bytes = (size_t)lv.batch * lv.channels * lv.height[l] * lv.width[l] * dtype_size(dtype);
+      if (bytes) B200DET_CUDA_OK(cudaMemsetAsync(lv.ptr[l], 0, bytes, st));
+    }
+  }
+  if (K * lv.channels * PH * PW == 0) return 0;
+  if (!rois || !grad || !gs) return fail(B200DET_EINVAL, "roi_align backward: null pointer");
+  int taken = 0;
+  int rc = roi_align_bwd_fast(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr,
+                              aligned != 0, st, &taken);
+  if (rc != 0 || taken) return rc;
+  return roi_align_bwd_generic(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr,
+                               aligned != 0, st);
+}
+
+}  // namespace b200det
+
+using namespace b200det;
+
+extern "C" {
+
+int b200det_version(void) { return B200DET_VERSION; }
+const char* b200det_last_error(void) { return g_err; }
+
+int b200det_roi_align_forward(const void* input, int in_layout, const void* rois, void* output,
+                              int out_layout, int dtype, int64_t N, int64_t C, int64_t H,
+                              int64_t W, int64_t K, int64_t PH, int64_t PW, double spatial_scale,
+                              int sampling_ratio, int aligned, void* stream) {
+  int rc = check_common("roi_align_forward", dtype, in_layout, out_layout, N, C, K, PH, PW);
+  if (rc) return rc;
+  LevelArgs lv;
+  const void* feats[1] = {input};
+  rc = fill_levels("roi_align_forward", lv, feats, &H, &W, &spatial_scale, 1, in_layout, N, C);
+  if (rc) return rc;
+  return forward_impl(lv, dtype, rois, nullptr, output, out_layout, K, PH, PW, sampling_ratio,
+                      aligned, (cudaStream_t)stream);
+}
+
+int b200det_roi_align_backward(const void* grad, const int64_t* grad_strides, const void* rois,
+                               void* grad_input, int gi_layout, int dtype, int64_t N, int64_t C,
+                               int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+                               double spatial_scale, int sampling_ratio, int aligned,
+                               int zero_init, void* stream) {
+  int rc = check_common("roi_align_backward", dtype, gi_layout, gi_layout, N, C, K, PH, PW);
+  if (rc) return rc;
+  LevelArgs lv;
+  const void* feats[1] = {grad_input};
+  rc = fill_levels("roi_align_backward", lv, feats, &H, &W, &spatial_scale, 1, gi_layout, N, C);
+  if (rc) return rc;
+  return backward_impl(lv, dtype, grad, grad_strides, rois, nullptr, K, PH, PW, sampling_ratio,
+                       aligned, zero_init, (cudaStream_t)stream);
+}
+
+int b200det_fpn_level_map(const void* rois, int dtype, int64_t K, int k_min, int k_max,
+                          int canonical_scale, int canonical_level, double eps, int32_t* levels,
+                          void* stream) {
+  if (K < 0) return fail(B200DET_EINVAL, "fpn_level_map: negative K");
+  if (K == 0) return 0;
+  if (!rois || !levels) return fail(B200DET_EINVAL, "fpn_level_map: null pointer");
+  return fpn_level_map(rois, dtype, K, k_min, k_max, canonical_scale, canonical_level, eps, levels,
+                       (cudaStream_t)stream);
+}
+
+int b200det_msroi_align_forward(const void* const* feats, const int64_t* heights,
+                                const int64_t* widths, const double* scales, int num_levels,
+                                int layout, const void* rois, int32_t* levels, int levels_given,
+                                void* output, int out_layout, int dtype, int64_t N, int64_t C,
+                                int64_t K, int64_t PH, int64_t PW, int sampling_ratio, int aligned,
+                                int k_min, int k_max, int canonical_scale, int canonical_level,
+                                double eps, void* stream) {
+  int rc = check_common("msroi_align_forward", dtype, layout, out_layout, N, C, K, PH, PW);
+  if (rc) return rc;
+  if (!feats || !heights || !widths || !scales)
+    return fail(B200DET_EINVAL, "msroi_align_forward: null level arrays");
+  LevelArgs lv;
+  rc = fill_levels("msroi_align_forward", lv, feats, heights, widths, scales, num_levels, layout, N, C);
+  if (rc) return rc;
+  const int32_t* lv_ids = nullptr;
+  if (num_levels > 1) {
+    if (K > 0 && !levels) return fail(B200DET_EINVAL, "msroi_align_forward: levels buffer required");
+    if (!levels_given && K > 0) {
+      rc = fpn_level_map(rois, dtype, K, k_min, k_max, canonical_scale, canonical_level, eps, levels,
+                         (cudaStream_t)stream);
+      if (rc) return rc;
+    }
+    lv_ids = levels;
+  }
+  return forward_impl(lv, dtype, rois, lv_ids, output, out_layout, K, PH, PW, sampling_ratio,
+                      aligned, (cudaStream_t)stream);
+}
+
+int b200det_msroi_align_backward(const void* grad, const int64_t* grad_strides, const void* rois,
+                                 const int32_t* levels, void* const* grad_feats,
+                                 const int64_t* heights, const int64_t* widths,
+                                 const double* scales, int num_levels, int layout, int dtype,
+                                 int64_t N, int64_t C, int64_t K, int64_t PH, int64_t PW,
+                                 int sampling_ratio, int aligned, int zero_init, void* stream) {
+  int rc = check_common("msroi_align_backward", dtype, layout, layout, N, C, K, PH, PW);
+  if (rc) return rc;
+  if (!grad_feats || !heights || !widths || !scales)
+    return fail(B200DET_EINVAL, "msroi_align_backward: null level arrays");
+  LevelArgs lv;
+  rc = fill_levels("msroi_align_backward", lv, (const void* const*)grad_feats, heights, widths,
+                   scales, num_levels, layout, N, C);
+  if (rc) return rc;
+  if (num_levels > 1 && K > 0 && !levels)
+    return fail(B200DET_EINVAL, "msroi_align_backward: levels required");
+  return backward_impl(lv, dtype, grad, grad_strides, rois, num_levels > 1 ? levels : nullptr, K, PH,
+                       PW, sampling_ratio, aligned, zero_init, (cudaStream_t)stream);
+}
+
+size_t b200det_nms_workspace_bytes(int64_t N) { return nms_workspace_bytes(N); }
+
+int b200det_nms(const void* boxes, const void* scores, int dtype, int64_t N, double iou_threshold,
+                int64_t* keep, int64_t* num_keep, void* workspace, size_t workspace_bytes,
+                void* stream) {
+  if (N < 0) return fail(B200DET_EINVAL, "nms: negative N");
+  if (!num_keep) return fail(B200DET_EINVAL, "nms: null num_keep");
+  if (N > 0 && (!boxes || !scores || !keep || !workspace)) return fail(B200DET_EINVAL, "nms: null pointer");
+  if (dtype_size(dtype) == 0) return fail(B200DET_ENOSUP, "nms: unknown dtype %d", dtype);
+  return nms_device(boxes, scores, nullptr, dtype, N, iou_threshold, 0, keep, num_keep, workspace,
+                    workspace_bytes, (cudaStream_t)stream);
+}
+
+int b200det_batched_nms(const void* boxes, const void* scores, const int64_t* idxs, int dtype,
+                        int64_t N, double iou_threshold, int mode, int64_t* keep,
+                        int64_t* num_keep, void* workspace, size_t workspace_bytes, void* stream) {
+  if (N < 0) return fail(B200DET_EINVAL, "batched_nms: negative N");
+  if (!num_keep) return fail(B200DET_EINVAL, "batched_nms: null num_keep");
+  if (N > 0 && (!boxes || !scores || !idxs || !keep || !workspace))
+    return fail(B200DET_EINVAL, "batched_nms: null pointer");
+  if (dtype_size(dtype) == 0) return fail(B200DET_ENOSUP, "batched_nms: unknown dtype %d", dtype);
+  int m;
+  if (mode == B200DET_BNMS_AUTO) m = (4 * N > 20000) ? 2 : 1;  // boxes.py:72, CUDA rule
+  else if (mode == B200DET_BNMS_COORD_TRICK) m = 1;
+  else if (mode == B200DET_BNMS_VANILLA) m = 2;
+  else return fail(B200DET_EINVAL, "batched_nms: unknown mode %d", mode);
+  return nms_device(boxes, scores, idxs, dtype, N, iou_threshold, m, keep, num_keep, workspace,
+                    workspace_bytes, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,192 @@
+// host_api.cu -- host-buffer entry points (b200det_*_host): what a caller that
+// holds CPU tensors (the reference's CPU dispatch key,
+// torchvision/csrc/ops/cpu/roi_align_kernel.cpp:282-386, cpu/nms_kernel.cpp:79-108)
+// binds to.  Each call copies its operands into a per-process device arena,
+// runs the device entry points of c_api.cu on a private stream and copies the
+// results back before returning.  Pinned caller buffers get full PCIe rate;
+// pageable ones work at whatever cudaMemcpyAsync's internal staging gives.
+#include <mutex>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200det {
+namespace {
+
+struct Arena {
+  int device = -1;
+  cudaStream_t stream = nullptr;
+  void* buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t cap[6] = {0, 0, 0, 0, 0, 0};
+  void* pinned = nullptr;  // small bounce buffer for counts
+};
+
+Arena g_arena;
+std::mutex g_mu;
+
+int arena_bind(int device) {
+  if (g_arena.device != device) {
+    if (g_arena.device >= 0) {
+      cudaSetDevice(g_arena.device);
+      for (int i = 0; i < 6; ++i) { if (g_arena.buf[i]) cudaFree(g_arena.buf[i]); g_arena.buf[i] = nullptr; g_arena.cap[i] = 0; }
+      if (g_arena.stream) cudaStreamDestroy(g_arena.stream);
+      if (g_arena.pinned) cudaFreeHost(g_arena.pinned);
+      g_arena = Arena();
+    }
+    B200DET_CUDA_OK(cudaSetDevice(device));
+    B200DET_CUDA_OK(cudaStreamCreateWithFlags(&g_arena.stream, cudaStreamNonBlocking));
+    B200DET_CUDA_OK(cudaMallocHost(&g_arena.pinned, 256));
+    g_arena.device = device;
+  } else {
+    B200DET_CUDA_OK(cudaSetDevice(device));
+  }
+  return 0;
+}
+
+int arena_get(int slot, size_t bytes, void** out) {
+  if (bytes == 0) bytes = 256;
+  if (g_arena.cap[slot] < bytes) {
+    if (g_arena.buf[slot]) B200DET_CUDA_OK(cudaFree(g_arena.buf[slot]));
+    g_arena.buf[slot] = nullptr;
+    g_arena.cap[slot] = 0;
+    const size_t want = bytes + bytes / 8;
+    B200DET_CUDA_OK(cudaMalloc(&g_arena.buf[slot], want));
+    g_arena.cap[slot] = want;
+  }
+  *out = g_arena.buf[slot];
+  return 0;
+}
+
+}  // namespace
+}  // namespace b200det
+
+using namespace b200det;
+
+extern "C" {
+
+int b200det_roi_align_forward_host(const void* input, int in_layout, const void* rois, void* output,
+                                   int out_layout, int dtype, int64_t N, int64_t C, int64_t H,
+                                   int64_t W, int64_t K, int64_t PH, int64_t PW,
+                                   double spatial_scale, int sampling_ratio, int aligned,
+                                   int device) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  const size_t es = dtype_size(dtype);
+  if (!es) return fail(B200DET_ENOSUP, "roi_align_forward_host: unknown dtype %d", dtype);
+  if (N < 0 || C < 0 || H < 0 || W < 0 || K < 0 || PH < 0 || PW < 0)
+    return fail(B200DET_EINVAL, "roi_align_forward_host: negative size");
+  int rc = arena_bind(device);
+  if (rc) return rc;
+  const size_t in_b = (size_t)N * C * H * W * es, roi_b = (size_t)K * 5 * (dtype == B200DET_F64 ? 8 : 4),
+               out_b = (size_t)K * C * PH * PW * es;
+  void *d_in, *d_roi, *d_out;
+  if ((rc = arena_get(0, in_b, &d_in)) || (rc = arena_get(1, roi_b, &d_roi)) ||
+      (rc = arena_get(2, out_b, &d_out)))
+    return rc;
+  cudaStream_t st = g_arena.stream;
+  if (in_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_in, input, in_b, cudaMemcpyHostToDevice, st));
+  if (roi_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_roi, rois, roi_b, cudaMemcpyHostToDevice, st));
+  rc = b200det_roi_align_forward(d_in, in_layout, d_roi, d_out, out_layout, dtype, N, C, H, W, K, PH,
+                                 PW, spatial_scale, sampling_ratio, aligned, st);
+  if (rc) return rc;
+  if (out_b) B200DET_CUDA_OK(cudaMemcpyAsync(output, d_out, out_b, cudaMemcpyDeviceToHost, st));
+  B200DET_CUDA_OK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int b200det_roi_align_backward_host(const void* grad, const int64_t* grad_strides,
+                                    int64_t grad_span_elems, const void* rois, void* grad_input,
+                                    int gi_layout, int dtype, int64_t N, int64_t C, int64_t H,
+                                    int64_t W, int64_t K, int64_t PH, int64_t PW,
+                                    double spatial_scale, int sampling_ratio, int aligned,
+                                    int device) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  const size_t es = dtype_size(dtype);
+  if (!es) return fail(B200DET_ENOSUP, "roi_align_backward_host: unknown dtype %d", dtype);
+  if (N < 0 || C < 0 || H < 0 || W < 0 || K < 0 || PH < 0 || PW < 0 || grad_span_elems < 0)
+    return fail(B200DET_EINVAL, "roi_align_backward_host: negative size");
+  int rc = arena_bind(device);
+  if (rc) return rc;
+  const size_t g_b = (size_t)grad_span_elems * es, roi_b = (size_t)K * 5 * (dtype == B200DET_F64 ? 8 : 4),
+               gi_b = (size_t)N * C * H * W * es;
+  void *d_g, *d_roi, *d_gi;
+  if ((rc = arena_get(0, gi_b, &d_gi)) || (rc = arena_get(1, roi_b, &d_roi)) ||
+      (rc = arena_get(2, g_b, &d_g)))
+    return rc;
+  cudaStream_t st = g_arena.stream;
+  if (g_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_g, grad, g_b, cudaMemcpyHostToDevice, st));
+  if (roi_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_roi, rois, roi_b, cudaMemcpyHostToDevice, st));
+  rc = b200det_roi_align_backward(d_g, grad_strides, d_roi, d_gi, gi_layout, dtype, N, C, H, W, K,
+                                  PH, PW, spatial_scale, sampling_ratio, aligned, 1, st);
+  if (rc) return rc;
+  if (gi_b) B200DET_CUDA_OK(cudaMemcpyAsync(grad_input, d_gi, gi_b, cudaMemcpyDeviceToHost, st));
+  B200DET_CUDA_OK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+static int nms_host_common(const void* boxes, const void* scores, const int64_t* idxs, int dtype,
+                           int64_t N, double thr, int mode, int64_t* keep, int64_t* num_keep,
+                           int device) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  const size_t es = dtype_size(dtype);
+  if (!es) return fail(B200DET_ENOSUP, "nms_host: unknown dtype %d", dtype);
+  if (N < 0) return fail(B200DET_EINVAL, "nms_host: negative N");
+  if (!num_keep) return fail(B200DET_EINVAL, "nms_host: null num_keep");
+  if (N == 0) { *num_keep = 0; return 0; }
+  int rc = arena_bind(device);
+  if (rc) return rc;
+  const size_t ws_b = b200det_nms_workspace_bytes(N);
+  void *d_boxes, *d_scores, *d_idx, *d_keep, *d_ws;
+  if ((rc = arena_get(0, (size_t)N * 4 * es, &d_boxes)) || (rc = arena_get(1, (size_t)N * es, &d_scores)) ||
+      (rc = arena_get(2, (size_t)N * 8, &d_idx)) || (rc = arena_get(3, (size_t)(N + 1) * 8, &d_keep)) ||
+      (rc = arena_get(4, ws_b, &d_ws)))
+    return rc;
+  cudaStream_t st = g_arena.stream;
+  B200DET_CUDA_OK(cudaMemcpyAsync(d_boxes, boxes, (size_t)N * 4 * es, cudaMemcpyHostToDevice, st));
+  B200DET_CUDA_OK(cudaMemcpyAsync(d_scores, scores, (size_t)N * es, cudaMemcpyHostToDevice, st));
+  int64_t* d_cnt = (int64_t*)d_keep + N;
+  if (idxs) {
+    B200DET_CUDA_OK(cudaMemcpyAsync(d_idx, idxs, (size_t)N * 8, cudaMemcpyHostToDevice, st));
+    rc = b200det_batched_nms(d_boxes, d_scores, (const int64_t*)d_idx, dtype, N, thr, mode,
+                             (int64_t*)d_keep, d_cnt, d_ws, ws_b, st);
+  } else {
+    rc = b200det_nms(d_boxes, d_scores, dtype, N, thr, (int64_t*)d_keep, d_cnt, d_ws, ws_b, st);
+  }
+  if (rc) return rc;
+  // one copy brings back indices and the trailing count
+  int64_t* bounce = nullptr;
+  B200DET_CUDA_OK(cudaMemcpyAsync(g_arena.pinned, d_cnt, 8, cudaMemcpyDeviceToHost, st));
+  B200DET_CUDA_OK(cudaStreamSynchronize(st));
+  bounce = (int64_t*)g_arena.pinned;
+  *num_keep = bounce[0];
+  if (*num_keep > 0)
+    B200DET_CUDA_OK(cudaMemcpy(keep, d_keep, (size_t)(*num_keep) * 8, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int b200det_nms_host(const void* boxes, const void* scores, int dtype, int64_t N,
+                     double iou_threshold, int64_t* keep, int64_t* num_keep, int device) {
+  return nms_host_common(boxes, scores, nullptr, dtype, N, iou_threshold, 0, keep, num_keep, device);
+}
+
+int b200det_batched_nms_host(const void* boxes, const void* scores, const int64_t* idxs, int dtype,
+                             int64_t N, double iou_threshold, int mode, int64_t* keep,
+                             int64_t* num_keep, int device) {
+  if (!idxs && N > 0) return fail(B200DET_EINVAL, "batched_nms_host: null idxs");
+  return nms_host_common(boxes, scores, idxs, dtype, N, iou_threshold, mode, keep, num_keep, device);
+}
+
+void b200det_host_release(void) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  if (g_arena.device < 0) return;
+  cudaSetDevice(g_arena.device);
+  for (int i = 0; i < 6; ++i) {
+    if (g_arena.buf[i]) cudaFree(g_arena.buf[i]);
+    g_arena.buf[i] = nullptr;
+    g_arena.cap[i] = 0;
+  }
+  if (g_arena.stream) cudaStreamDestroy(g_arena.stream);
+  if (g_arena.pinned) cudaFreeHost(g_arena.pinned);
+  g_arena = Arena();
+}
+
+}  // extern "C"

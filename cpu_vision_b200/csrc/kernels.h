@@ -1,0 +1,49 @@
+// kernels.h -- internal launch interface between c_api.cu and the kernel files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200_detection_ops.h"
+
+namespace b200det {
+
+// host-side description of the feature pyramid one call works on
+struct LevelArgs {
+  void* ptr[B200DET_MAX_LEVELS];
+  int64_t height[B200DET_MAX_LEVELS];
+  int64_t width[B200DET_MAX_LEVELS];
+  double scale[B200DET_MAX_LEVELS];
+  int num_levels;
+  int layout;        // b200det_layout of every level
+  int64_t batch;     // N
+  int64_t channels;  // C
+};
+
+size_t dtype_size(int dtype);
+
+// roi_align_generic.cu
+int roi_align_fwd_generic(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
+                          void* out, int out_layout, long long K, int PH, int PW, int sr,
+                          bool aligned, cudaStream_t st);
+int roi_align_bwd_generic(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
+                          const void* rois, const int32_t* levels, long long K, int PH, int PW,
+                          int sr, bool aligned, cudaStream_t st);
+int fpn_level_map(const void* rois, int dtype, long long K, int k_min, int k_max, int s0, int lvl0,
+                  double eps, int32_t* levels, cudaStream_t st);
+
+// roi_align_fast.cu: returns 1 when it took the call, 0 when the generic path
+// must run, <0 / >0 on error like the public API.
+int roi_align_fwd_fast(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
+                       void* out, int out_layout, long long K, int PH, int PW, int sr,
+                       bool aligned, cudaStream_t st, int* taken);
+int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
+                       const void* rois, const int32_t* levels, long long K, int PH, int PW,
+                       int sr, bool aligned, cudaStream_t st, int* taken);
+
+// nms_sm100.cu
+size_t nms_workspace_bytes(long long N);
+int nms_device(const void* boxes, const void* scores, const int64_t* idxs, int dtype, long long N,
+               double thr, int mode, int64_t* keep, int64_t* num_keep, void* ws, size_t ws_bytes,
+               cudaStream_t st);
+
+}  // namespace b200det

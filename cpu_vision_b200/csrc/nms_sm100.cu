@@ -1,0 +1,374 @@
+// nms_sm100.cu -- greedy NMS and class-aware NMS, entirely on the device.
+//
+// Pipeline (all on the caller's stream, no host round trip):
+//   1. nms_prepare_kernel   scores -> fp32 sort keys, iota indices
+//                           (+ per-class coordinate offsets for the
+//                           coordinate-trick mode, torchvision/ops/boxes.py:91-93)
+//   2. cub::DeviceRadixSort::SortPairsDescending   stable, ties keep ascending
+//                           original index like scores.sort(stable=True,
+//                           descending=True) (cuda/nms_kernel.cu:112-113)
+//   3. nms_gather_kernel    boxes in score order, widened to the compare type
+//   4. nms_mask_kernel      upper-triangular 64x64 IoU>thr bit tiles
+//                           (replaces nms_kernel_impl, cuda/nms_kernel.cu:31-78)
+//   5. nms_scan_kernel      greedy keep scan on the device, one CTA
+//                           (replaces the D2H copy + host loop, :136-159) and
+//                           writes keep[] = order[kept] and the count.
+//
+// IoU follows devIoU (cuda/nms_kernel.cu:16-29) with every operation an
+// explicit round-to-nearest intrinsic so no FMA contraction can change a
+// comparison: inter / ((Sa + Sb) - inter) > (float)threshold.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200det {
+
+namespace {
+
+typedef unsigned long long u64;
+constexpr int kTile = 64;
+
+struct alignas(16) Box4f { float x1, y1, x2, y2; };
+struct alignas(32) Box4d { double x1, y1, x2, y2; };
+
+__device__ __forceinline__ bool iou_gt(const Box4f& a, const Box4f& b, float thr) {
+  const float left = fmaxf(a.x1, b.x1), right = fminf(a.x2, b.x2);
+  const float top = fmaxf(a.y1, b.y1), bottom = fminf(a.y2, b.y2);
+  const float w = fmaxf(__fsub_rn(right, left), 0.f), h = fmaxf(__fsub_rn(bottom, top), 0.f);
+  const float inter = __fmul_rn(w, h);
+  const float sa = __fmul_rn(__fsub_rn(a.x2, a.x1), __fsub_rn(a.y2, a.y1));
+  const float sb = __fmul_rn(__fsub_rn(b.x2, b.x1), __fsub_rn(b.y2, b.y1));
+  return __fdiv_rn(inter, __fsub_rn(__fadd_rn(sa, sb), inter)) > thr;
+}
+__device__ __forceinline__ bool iou_gt(const Box4d& a, const Box4d& b, float thr) {
+  const double left = fmax(a.x1, b.x1), right = fmin(a.x2, b.x2);
+  const double top = fmax(a.y1, b.y1), bottom = fmin(a.y2, b.y2);
+  const double w = fmax(__dsub_rn(right, left), 0.), h = fmax(__dsub_rn(bottom, top), 0.);
+  const double inter = __dmul_rn(w, h);
+  const double sa = __dmul_rn(__dsub_rn(a.x2, a.x1), __dsub_rn(a.y2, a.y1));
+  const double sb = __dmul_rn(__dsub_rn(b.x2, b.x1), __dsub_rn(b.y2, b.y1));
+  return __ddiv_rn(inter, __dsub_rn(__dadd_rn(sa, sb), inter)) > (double)thr;
+}
+
+template <typename T> struct BoxOf { using type = Box4f; };
+template <> struct BoxOf<double> { using type = Box4d; };
+
+// ---- 1. keys / iota / (optional) max coordinate ----------------------------
+template <typename T>
+__global__ void nms_prepare_kernel(const T* __restrict__ scores, long long n,
+                                   float* __restrict__ keys, int32_t* __restrict__ idx) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  keys[i] = (float)Io<T>::ld(scores + i);
+  idx[i] = (int32_t)i;
+}
+// fp64 scores cannot be ranked through fp32 keys without changing ties; they
+// get a 64-bit key path.
+__global__ void nms_prepare_kernel_f64(const double* __restrict__ scores, long long n,
+                                       double* __restrict__ keys, int32_t* __restrict__ idx) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  keys[i] = scores[i];
+  idx[i] = (int32_t)i;
+}
+
+// boxes.max() for the coordinate trick (boxes.py:91): one CTA, fp32 compare.
+template <typename T>
+__global__ void nms_max_coord_kernel(const T* __restrict__ boxes, long long n4,
+                                     typename Io<T>::acc* __restrict__ out) {
+  using A = typename Io<T>::acc;
+  __shared__ A red[32];
+  A m = -INFINITY;
+  bool nan = false;
+  for (long long i = threadIdx.x; i < n4; i += blockDim.x) {
+    const A v = Io<T>::ld(boxes + i);
+    nan |= (v != v);
+    m = v > m ? v : m;
+  }
+  if (nan) m = NAN;  // torch.max propagates NaN
+  for (int o = 16; o > 0; o >>= 1) {
+    const A other = __shfl_xor_sync(0xffffffffu, m, o);
+    m = (other != other || m != m) ? (A)NAN : (other > m ? other : m);
+  }
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    m = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : (A)-INFINITY;
+    for (int o = 16; o > 0; o >>= 1) {
+      const A other = __shfl_xor_sync(0xffffffffu, m, o);
+      m = (other != other || m != m) ? (A)NAN : (other > m ? other : m);
+    }
+    if (threadIdx.x == 0) *out = m;
+  }
+}
+
+// ---- 3. gather into score order ---------------------------------------------
+// mode: 0 plain, 1 coordinate trick (adds idxs*(max+1) with the reference's
+// fp32 rounding: boxes.py:92-93), 2 vanilla (keeps class id beside the box).
+template <typename T>
+__global__ void nms_gather_kernel(const T* __restrict__ boxes, const int64_t* __restrict__ idxs,
+                                  const int32_t* __restrict__ order, long long n, int mode,
+                                  const typename Io<T>::acc* __restrict__ max_coord,
+                                  typename BoxOf<T>::type* __restrict__ sorted,
+                                  int32_t* __restrict__ sorted_cls) {
+  using A = typename Io<T>::acc;
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const long long src = order[i];
+  A x1 = Io<T>::ld(boxes + src * 4 + 0), y1 = Io<T>::ld(boxes + src * 4 + 1);
+  A x2 = Io<T>::ld(boxes + src * 4 + 2), y2 = Io<T>::ld(boxes + src * 4 + 3);
+  if (mode == 1) {
+    // offsets = idxs.to(boxes) * (max_coordinate + 1); boxes + offsets[:, None]
+    // For fp16/bf16 boxes torch does this arithmetic in the boxes' dtype and
+    // nms then runs in that dtype; we are only exact for fp32/fp64 here and
+    // follow the autocast (fp32) semantics for the 16-bit types.
+    const A off = Ar<A>::mul((A)idxs[src], Ar<A>::add(*max_coord, (A)1));
+    x1 = Ar<A>::add(x1, off); y1 = Ar<A>::add(y1, off);
+    x2 = Ar<A>::add(x2, off); y2 = Ar<A>::add(y2, off);
+  }
+  typename BoxOf<T>::type b;
+  b.x1 = x1; b.y1 = y1; b.x2 = x2; b.y2 = y2;
+  sorted[i] = b;
+  if (sorted_cls) sorted_cls[i] = (int32_t)idxs[src];
+}
+
+// ---- 4. IoU bit tiles ---------------------------------------------------------
+// grid = (col_blocks, col_blocks); tiles below the diagonal exit at once and
+// their words are never read (the scan starts at the diagonal word).
+template <typename BoxT>
+__global__ void __launch_bounds__(kTile) nms_mask_kernel(int n, float thr,
+                                                         const BoxT* __restrict__ boxes,
+                                                         const int32_t* __restrict__ cls,
+                                                         u64* __restrict__ mask) {
+  const int row_start = blockIdx.y, col_start = blockIdx.x;
+  if (row_start > col_start) return;
+  const int row_size = min(n - row_start * kTile, kTile);
+  const int col_size = min(n - col_start * kTile, kTile);
+  __shared__ BoxT cb[kTile];
+  __shared__ int32_t cc[kTile];
+  if ((int)threadIdx.x < col_size) {
+    cb[threadIdx.x] = boxes[kTile * col_start + threadIdx.x];
+    cc[threadIdx.x] = cls ? cls[kTile * col_start + threadIdx.x] : 0;
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < row_size) {
+    const int cur = kTile * row_start + threadIdx.x;
+    const BoxT a = boxes[cur];
+    const int32_t ac = cls ? cls[cur] : 0;
+    u64 t = 0;
+    const int start = (row_start == col_start) ? threadIdx.x + 1 : 0;
+    for (int i = start; i < col_size; ++i)
+      if (cc[i] == ac && iou_gt(a, cb[i], thr)) t |= 1ULL << i;
+    const int col_blocks = (n + kTile - 1) / kTile;
+    mask[(long long)cur * col_blocks + col_start] = t;
+  }
+}
+
+// ---- 5. greedy scan -----------------------------------------------------------
+// One CTA walks the 64-box blocks in score order.  remv[] (one bit per box)
+// lives in shared memory; for block b thread 0 resolves the 64 in-block
+// decisions from the diagonal words, then all threads OR the kept rows into
+// the words to the right.  Finally the kept bits are compacted into keep[].
+constexpr int kScanThreads = 1024;
+
+__global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
+    const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
+    int64_t* __restrict__ keep, int64_t* __restrict__ num_keep) {
+  extern __shared__ u64 smem[];
+  u64* remv = smem;                 // [col_blocks]
+  u64* keptw = smem + col_blocks;   // [col_blocks]
+  __shared__ u64 diag[kTile];
+  __shared__ u64 s_kept;
+  __shared__ int s_base[kScanThreads / 32];
+  const int tid = threadIdx.x;
+  for (int j = tid; j < col_blocks; j += kScanThreads) remv[j] = 0;
+  __syncthreads();
+
+  for (int b = 0; b < col_blocks; ++b) {
+    const int rows = min(n - b * kTile, kTile);
+    if (tid < kTile) diag[tid] = tid < rows ? mask[(long long)(b * kTile + tid) * col_blocks + b] : 0ULL;
+    __syncthreads();
+    if (tid == 0) {
+      u64 alive = ~remv[b];
+      if (rows < kTile) alive &= (1ULL << rows) - 1ULL;
+      u64 kept = 0;
+#pragma unroll
+      for (int i = 0; i < kTile; ++i) {
+        if ((alive >> i) & 1ULL) {
+          kept |= 1ULL << i;
+          alive &= ~diag[i];
+        }
+      }
+      s_kept = kept;
+      keptw[b] = kept;
+    }
+    __syncthreads();
+    const u64 kept = s_kept;
+    for (int j = b + 1 + tid; j < col_blocks; j += kScanThreads) {
+      u64 acc = remv[j];
+      u64 kk = kept;
+      while (kk) {
+        const int i = __ffsll((long long)kk) - 1;
+        kk &= kk - 1;
+        acc |= mask[(long long)(b * kTile + i) * col_blocks + j];
+      }
+      remv[j] = acc;
+    }
+    __syncthreads();
+  }
+
+  // compaction: running offset over words, kScanThreads words per pass
+  int running = 0;
+  for (int w0 = 0; w0 < col_blocks; w0 += kScanThreads) {
+    const int w = w0 + tid;
+    const u64 kw = w < col_blocks ? keptw[w] : 0ULL;
+    const int cnt = __popcll(kw);
+    // block exclusive scan of cnt
+    int incl = cnt;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((tid & 31) >= o) incl += v;
+    }
+    if ((tid & 31) == 31) s_base[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+      int v = tid < kScanThreads / 32 ? s_base[tid] : 0;
+      int inc2 = v;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, inc2, o);
+        if (tid >= o) inc2 += u;
+      }
+      s_base[tid] = inc2 - v;  // exclusive
+      if (tid == 31) s_kept = (u64)inc2;  // pass total
+    }
+    __syncthreads();
+    int pos = running + s_base[tid >> 5] + incl - cnt;
+    u64 kk = kw;
+    while (kk) {
+      const int i = __ffsll((long long)kk) - 1;
+      kk &= kk - 1;
+      keep[pos++] = (int64_t)order[w * kTile + i];
+    }
+    running += (int)s_kept;
+    __syncthreads();
+  }
+  if (tid == 0) *num_keep = running;
+}
+
+__global__ void nms_zero_count_kernel(int64_t* num_keep) { *num_keep = 0; }
+
+// ---- workspace carving --------------------------------------------------------
+struct Carve {
+  char* p; size_t off, cap;
+  void* take(size_t bytes) {
+    off = (off + 255) & ~(size_t)255;
+    void* r = p ? p + off : nullptr;
+    off += bytes;
+    return r;
+  }
+};
+
+size_t cub_temp_bytes(long long n, bool f64) {
+  size_t bytes = 0;
+  if (f64)
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, (const double*)nullptr, (double*)nullptr,
+                                              (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
+  else
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, (const float*)nullptr, (float*)nullptr,
+                                              (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
+  return bytes;
+}
+
+struct Layout {
+  void *keys_in, *keys_out, *cub_tmp, *sorted, *maxc;
+  int32_t *idx_in, *order, *cls;
+  u64* mask;
+  size_t cub_bytes, total;
+};
+
+Layout carve(void* ws, long long n) {
+  Layout L;
+  Carve c{(char*)ws, 0, 0};
+  const long long cb = (n + kTile - 1) / kTile;
+  L.keys_in = c.take(n * 8);
+  L.keys_out = c.take(n * 8);
+  L.idx_in = (int32_t*)c.take(n * 4);
+  L.order = (int32_t*)c.take(n * 4);
+  L.cls = (int32_t*)c.take(n * 4);
+  L.maxc = c.take(16);
+  L.sorted = c.take(n * sizeof(Box4d));
+  L.cub_bytes = cub_temp_bytes(n, true);
+  const size_t f32b = cub_temp_bytes(n, false);
+  if (f32b > L.cub_bytes) L.cub_bytes = f32b;
+  L.cub_tmp = c.take(L.cub_bytes);
+  L.mask = (u64*)c.take((size_t)n * cb * 8);
+  L.total = c.off + 256;
+  return L;
+}
+
+template <typename T>
+int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long n, double thr,
+          int mode, int64_t* keep, int64_t* num_keep, void* ws, cudaStream_t st) {
+  using A = typename Io<T>::acc;
+  using BoxT = typename BoxOf<T>::type;
+  const Layout L = carve(ws, n);
+  const int th = 256, bl = (int)((n + th - 1) / th);
+  const int col_blocks = (int)((n + kTile - 1) / kTile);
+  constexpr bool f64 = std::is_same<T, double>::value;
+  if (f64) {
+    nms_prepare_kernel_f64<<<bl, th, 0, st>>>((const double*)scores, n, (double*)L.keys_in, L.idx_in);
+    B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairsDescending(
+        L.cub_tmp, const_cast<size_t&>(L.cub_bytes), (const double*)L.keys_in, (double*)L.keys_out,
+        (const int32_t*)L.idx_in, L.order, (int)n, 0, 64, st));
+  } else {
+    nms_prepare_kernel<T><<<bl, th, 0, st>>>((const T*)scores, n, (float*)L.keys_in, L.idx_in);
+    B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairsDescending(
+        L.cub_tmp, const_cast<size_t&>(L.cub_bytes), (const float*)L.keys_in, (float*)L.keys_out,
+        (const int32_t*)L.idx_in, L.order, (int)n, 0, 32, st));
+  }
+  if (mode == 1)
+    nms_max_coord_kernel<T><<<1, 1024, 0, st>>>((const T*)boxes, n * 4, (A*)L.maxc);
+  nms_gather_kernel<T><<<bl, th, 0, st>>>((const T*)boxes, idxs, L.order, n, mode, (const A*)L.maxc,
+                                          (BoxT*)L.sorted, mode == 2 ? L.cls : nullptr);
+  dim3 grid(col_blocks, col_blocks);
+  nms_mask_kernel<BoxT><<<grid, kTile, 0, st>>>((int)n, (float)thr, (const BoxT*)L.sorted,
+                                               mode == 2 ? L.cls : nullptr, L.mask);
+  const size_t smem = (size_t)col_blocks * 16;
+  if (smem > 48 * 1024)
+    B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  nms_scan_kernel<<<1, kScanThreads, smem, st>>>(L.mask, (int)n, col_blocks, L.order, keep, num_keep);
+  B200DET_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+size_t nms_workspace_bytes(long long N) {
+  if (N <= 0) return 256;
+  return carve(nullptr, N).total;
+}
+
+int nms_device(const void* boxes, const void* scores, const int64_t* idxs, int dtype, long long N,
+               double thr, int mode, int64_t* keep, int64_t* num_keep, void* ws, size_t ws_bytes,
+               cudaStream_t st) {
+  if (N == 0) {
+    nms_zero_count_kernel<<<1, 1, 0, st>>>(num_keep);
+    B200DET_CUDA_OK(cudaGetLastError());
+    return 0;
+  }
+  if (N > 100000000LL / 1) return fail(B200DET_EINVAL, "nms: N=%lld too large", N);
+  if (ws_bytes < nms_workspace_bytes(N))
+    return fail(B200DET_EWORKSPACE, "nms: workspace %zu < required %zu", ws_bytes, nms_workspace_bytes(N));
+  const long long cb = (N + kTile - 1) / kTile;
+  if (cb * 16 > 200 * 1024) return fail(B200DET_ENOSUP, "nms: N=%lld exceeds the single-CTA scan capacity", N);
+  switch (dtype) {
+    case B200DET_F32: return nms_t<float>(boxes, scores, idxs, N, thr, mode, keep, num_keep, ws, st);
+    case B200DET_F16: return nms_t<__half>(boxes, scores, idxs, N, thr, mode, keep, num_keep, ws, st);
+    case B200DET_BF16: return nms_t<__nv_bfloat16>(boxes, scores, idxs, N, thr, mode, keep, num_keep, ws, st);
+    case B200DET_F64: return nms_t<double>(boxes, scores, idxs, N, thr, mode, keep, num_keep, ws, st);
+  }
+  return fail(B200DET_ENOSUP, "nms: unknown dtype %d", dtype);
+}
+
+}  // namespace b200det

@@ -1,0 +1,93 @@
+"""Shard-by-image multi-GPU harness.
+
+RoIs and boxes belong to exactly one image and images are independent, so the
+path shards with no data-path collective: rank r owns the contiguous image
+block [r*B/W, (r+1)*B/W), its feature maps, its RoIs (batch index rebased to
+the local block) and its per-image box sets.  The only exchange is optional
+and sits AFTER the kernels: an all-gather that reassembles pooled features and
+kept indices for a consumer that wants them on every rank.
+
+The reference has no counterpart inside the library (its only collectives are
+in references/detection/utils.py); these helpers are what its DDP recipes would
+call around torchvision.ops.
+"""
+from typing import List, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def image_block(num_images: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """[lo, hi) of the images rank owns; blocks differ by at most one image."""
+    base, rem = divmod(num_images, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def shard_rois(rois: torch.Tensor, num_images: int, rank: int, world_size: int):
+    """Select this rank's RoIs from a global Tensor[K,5] and rebase their batch index.
+
+    Returns (local_rois, global_row_index) -- the second lets the caller put
+    local results back at the global positions.
+    """
+    lo, hi = image_block(num_images, rank, world_size)
+    b = rois[:, 0]
+    sel = torch.nonzero((b >= lo) & (b < hi), as_tuple=False).flatten()
+    local = rois.index_select(0, sel).clone()
+    local[:, 0] -= lo
+    return local, sel
+
+
+def all_gather_rows(local: torch.Tensor, counts: Sequence[int] = None, group=None) -> torch.Tensor:
+    """Concatenate every rank's [k_r, ...] rows in rank order.
+
+    Equal k_r -> one all_gather_into_tensor straight into the result (each rank
+    can also have produced its rows in place: see gather_buffer()).  Unequal k_r
+    -> pad to the maximum, gather, and drop the padding.
+    """
+    world = dist.get_world_size(group)
+    if world == 1:
+        return local
+    local = local.contiguous()
+    if counts is None:
+        c = torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device)
+        allc = torch.empty(world, dtype=torch.int64, device=local.device)
+        dist.all_gather_into_tensor(allc, c, group=group)
+        counts = allc.tolist()
+    kmax = max(counts)
+    if all(c == kmax for c in counts):
+        out = torch.empty((world * kmax,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(out, local, group=group)
+        return out
+    padded = torch.zeros((kmax,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    padded[: local.shape[0]] = local
+    out = torch.empty((world * kmax,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, padded, group=group)
+    return torch.cat([out[r * kmax: r * kmax + counts[r]] for r in range(world)], dim=0)
+
+
+def gather_buffer(k_local: int, tail_shape: Sequence[int], dtype, device, rank: int, world_size: int,
+                  memory_format=torch.contiguous_format):
+    """Allocate the full [W*k_local, ...] gather target and return (full, my_slice).
+
+    The roi_align kernel writes straight into `my_slice`, so the all-gather
+    needs no staging copy: all_gather_into_tensor(full, my_slice) is in place.
+    """
+    full = torch.empty((world_size * k_local,) + tuple(tail_shape), dtype=dtype, device=device,
+                       memory_format=memory_format)
+    return full, full[rank * k_local: (rank + 1) * k_local]
+
+
+def all_gather_keep(keep: torch.Tensor, count: torch.Tensor, capacity: int, group=None) -> List[torch.Tensor]:
+    """Gather variable-length kept-index lists as (count, padded int64[capacity]) per rank."""
+    world = dist.get_world_size(group)
+    pack = torch.zeros(capacity + 1, dtype=torch.int64, device=keep.device)
+    pack[0] = count.reshape(())
+    n = min(int(keep.shape[0]), capacity)
+    pack[1: 1 + n] = keep[:n]
+    if world == 1:
+        return [pack[1: 1 + int(pack[0])]]
+    out = torch.empty(world * (capacity + 1), dtype=torch.int64, device=keep.device)
+    dist.all_gather_into_tensor(out, pack, group=group)
+    out = out.view(world, capacity + 1)
+    return [out[r, 1: 1 + int(out[r, 0])] for r in range(world)]

@@ -1,0 +1,211 @@
+/*
+ * b200_detection_ops.h -- C-ABI of the B200-native detection-head hot path.
+ *
+ * This is the drop-in boundary beneath the PyTorch dispatcher shim
+ * (cpu_vision_b200/csrc/torch_shim.cpp).  Every entry point takes plain
+ * pointers, sizes and a cudaStream_t passed as void*; no torch types appear.
+ * Nothing here allocates device memory unless the name ends in `_host`
+ * (those own a private staging arena, see below).
+ *
+ * Each function names the reference interface it replaces; paths are relative
+ * to the reference tree (kaisun24/CPU-Vision, a torchvision 0.20 fork).
+ *
+ * Return value: 0 on success, a positive cudaError_t from the CUDA runtime,
+ * or a negative B200DET_E* code for argument errors.  b200det_last_error()
+ * returns a thread-local message for the last non-zero return.
+ */
+#ifndef B200_DETECTION_OPS_H
+#define B200_DETECTION_OPS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200DET_VERSION 100 /* 0.1.0 */
+#define B200DET_MAX_LEVELS 8
+
+/* element type of feature maps / rois / boxes.  Arithmetic is fp32 for F32,
+ * F16 and BF16 I/O and fp64 for F64 (the reference dispatches double, float
+ * and half: torchvision/csrc/ops/cuda/roi_align_kernel.cu:376). */
+typedef enum {
+  B200DET_F32 = 0,
+  B200DET_F16 = 1,
+  B200DET_BF16 = 2,
+  B200DET_F64 = 3
+} b200det_dtype;
+
+/* memory order of a logically [N, C, H, W] tensor */
+typedef enum {
+  B200DET_NCHW = 0, /* torch.contiguous_format   */
+  B200DET_NHWC = 1  /* torch.channels_last (the B200-native fast path) */
+} b200det_layout;
+
+typedef enum {
+  B200DET_EINVAL = -1,   /* bad argument (null pointer, negative size, ...) */
+  B200DET_ENOSUP = -2,   /* unsupported dtype/layout combination           */
+  B200DET_EWORKSPACE = -3 /* workspace too small                           */
+} b200det_status;
+
+int b200det_version(void);
+const char* b200det_last_error(void);
+
+/* ------------------------------------------------------------------------
+ * RoIAlign
+ * --------------------------------------------------------------------- */
+
+/* Forward.  Replaces roi_align_forward_kernel
+ * (torchvision/csrc/ops/cuda/roi_align_kernel.cu:334-394; CPU twin
+ * torchvision/csrc/ops/cpu/roi_align_kernel.cpp:282-328).
+ *   input  : device, logical [N, C, H, W] in `in_layout`
+ *   rois   : device, [K, 5] rows (batch_index, x1, y1, x2, y2) in the
+ *            ARITHMETIC type of `dtype`: float for F32/F16/BF16 features,
+ *            double for F64.  (The reference demands rois.dtype ==
+ *            input.dtype, :350, and its autocast wrapper widens both to fp32,
+ *            autocast/roi_align_kernel.cpp:12-31; the shim widens 16-bit rois
+ *            the same way, so bf16/fp16 features keep full-precision boxes.)
+ *   output : device, logical [K, C, PH, PW] in `out_layout`; every element is
+ *            written (no pre-zeroing needed, unlike the reference's at::zeros)
+ * spatial_scale is converted to the arithmetic type before use, like the
+ * reference kernel argument (`const T spatial_scale`, :72). */
+int b200det_roi_align_forward(
+    const void* input, int in_layout, const void* rois, void* output,
+    int out_layout, int dtype, int64_t N, int64_t C, int64_t H, int64_t W,
+    int64_t K, int64_t PH, int64_t PW, double spatial_scale,
+    int sampling_ratio, int aligned, void* stream);
+
+/* Backward.  Replaces roi_align_backward_kernel
+ * (torchvision/csrc/ops/cuda/roi_align_kernel.cu:396-466; CPU twin
+ * torchvision/csrc/ops/cpu/roi_align_kernel.cpp:330-386).
+ *   grad         : device, logical [K, C, PH, PW] with ARBITRARY element
+ *                  strides grad_strides[4] = (k, c, ph, pw), as the reference
+ *                  honours (:253-256, :435-438)
+ *   grad_input   : device, logical [N, C, H, W] in `gi_layout`; zero-filled
+ *                  by this call when zero_init != 0, then accumulated into
+ *                  with red.global.add (non-deterministic order, as :440). */
+int b200det_roi_align_backward(
+    const void* grad, const int64_t* grad_strides, const void* rois,
+    void* grad_input, int gi_layout, int dtype, int64_t N, int64_t C,
+    int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+    double spatial_scale, int sampling_ratio, int aligned, int zero_init,
+    void* stream);
+
+/* FPN level mapper.  Replaces LevelMapper.__call__
+ * (torchvision/ops/poolers.py:73-84):
+ *   lvl = floor(canonical_level + log2(sqrt(area) / canonical_scale) + eps)
+ *   clamp to [k_min, k_max], minus k_min.
+ *   rois   : device [K, 5] (column 0 ignored), float (arithmetic type rule as
+ *            above; F64 is not supported here)
+ *   levels : device int32 [K] */
+int b200det_fpn_level_map(
+    const void* rois, int dtype, int64_t K, int k_min, int k_max,
+    int canonical_scale, int canonical_level, double eps, int32_t* levels,
+    void* stream);
+
+/* MultiScaleRoIAlign forward in ONE launch sequence.  Replaces the per-level
+ * loop of _multiscale_roi_align (torchvision/ops/poolers.py:146-227): level
+ * mapping, per-level where/gather, roi_align, and the index_put scatter back
+ * into original RoI order.
+ *   feats[l]   : device, logical [N, C, heights[l], widths[l]] in `layout`
+ *   scales[l]  : spatial scale of level l (poolers.py:98-134)
+ *   levels     : device int32 [K] scratch/out; filled by this call through
+ *                b200det_fpn_level_map unless levels_given != 0
+ *   output     : device, logical [K, C, PH, PW] in `out_layout`, RoI order kept
+ * The reference calls roi_align with aligned=False here (poolers.py:204-210);
+ * `aligned` is still a parameter so both are reachable. */
+int b200det_msroi_align_forward(
+    const void* const* feats, const int64_t* heights, const int64_t* widths,
+    const double* scales, int num_levels, int layout, const void* rois,
+    int32_t* levels, int levels_given, void* output, int out_layout, int dtype,
+    int64_t N, int64_t C, int64_t K, int64_t PH, int64_t PW,
+    int sampling_ratio, int aligned, int k_min, int k_max,
+    int canonical_scale, int canonical_level, double eps, void* stream);
+
+/* MultiScaleRoIAlign backward: the autograd transpose of the call above.
+ *   grad_feats[l] : device, logical [N, C, heights[l], widths[l]] in `layout`,
+ *                   zero-filled here when zero_init != 0
+ *   levels        : device int32 [K], as produced by the forward */
+int b200det_msroi_align_backward(
+    const void* grad, const int64_t* grad_strides, const void* rois,
+    const int32_t* levels, void* const* grad_feats, const int64_t* heights,
+    const int64_t* widths, const double* scales, int num_levels, int layout,
+    int dtype, int64_t N, int64_t C, int64_t K, int64_t PH, int64_t PW,
+    int sampling_ratio, int aligned, int zero_init, void* stream);
+
+/* ------------------------------------------------------------------------
+ * NMS
+ * --------------------------------------------------------------------- */
+
+typedef enum {
+  B200DET_BNMS_AUTO = -1,   /* reference rule for CUDA tensors: vanilla when
+                               4*N > 20000 (torchvision/ops/boxes.py:72)     */
+  B200DET_BNMS_COORD_TRICK = 0, /* _batched_nms_coordinate_trick, boxes.py:78-95 */
+  B200DET_BNMS_VANILLA = 1      /* _batched_nms_vanilla, boxes.py:98-112        */
+} b200det_bnms_mode;
+
+/* Bytes of device scratch b200det_nms / b200det_batched_nms need for N boxes. */
+size_t b200det_nms_workspace_bytes(int64_t N);
+
+/* Greedy NMS, everything on the device (no D2H round trip, unlike the
+ * reference's mask.to(kCPU) + host scan).  Replaces nms_kernel
+ * (torchvision/csrc/ops/cuda/nms_kernel.cu:80-165; CPU twin
+ * torchvision/csrc/ops/cpu/nms_kernel.cpp:9-108).
+ *   boxes    : device [N, 4] (x1, y1, x2, y2); scores: device [N]; same dtype
+ *   keep     : device int64 [N] capacity; the first *num_keep entries are the
+ *              kept ORIGINAL indices in descending-score order (stable ties)
+ *   num_keep : device int64 [1]
+ * IoU is evaluated in fp32 as (inter / ((Sa + Sb) - inter)) > (float)thr,
+ * like devIoU (nms_kernel.cu:16-29). */
+int b200det_nms(
+    const void* boxes, const void* scores, int dtype, int64_t N,
+    double iou_threshold, int64_t* keep, int64_t* num_keep, void* workspace,
+    size_t workspace_bytes, void* stream);
+
+/* Class-aware NMS in one pass.  Replaces batched_nms
+ * (torchvision/ops/boxes.py:44-112).
+ *   idxs : device int64 [N] category of each box
+ *   mode : b200det_bnms_mode.  COORD_TRICK reproduces the fp32 rounding of
+ *          `boxes + idxs.to(boxes) * (boxes.max() + 1)`; VANILLA compares the
+ *          unshifted boxes class by class. */
+int b200det_batched_nms(
+    const void* boxes, const void* scores, const int64_t* idxs, int dtype,
+    int64_t N, double iou_threshold, int mode, int64_t* keep,
+    int64_t* num_keep, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Host-buffer entry points (what a CPU-tensor caller of the reference binds).
+ * Inputs and outputs are HOST pointers; the call stages them through a
+ * per-process device arena (grown on demand, pinned bounce buffers), runs the
+ * kernels above on `device` and returns after the results are in host memory.
+ * b200det_host_release() frees the arena.
+ * --------------------------------------------------------------------- */
+
+int b200det_roi_align_forward_host(
+    const void* input, int in_layout, const void* rois, void* output,
+    int out_layout, int dtype, int64_t N, int64_t C, int64_t H, int64_t W,
+    int64_t K, int64_t PH, int64_t PW, double spatial_scale,
+    int sampling_ratio, int aligned, int device);
+
+int b200det_roi_align_backward_host(
+    const void* grad, const int64_t* grad_strides, int64_t grad_span_elems,
+    const void* rois, void* grad_input, int gi_layout, int dtype, int64_t N,
+    int64_t C, int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+    double spatial_scale, int sampling_ratio, int aligned, int device);
+
+int b200det_nms_host(
+    const void* boxes, const void* scores, int dtype, int64_t N,
+    double iou_threshold, int64_t* keep, int64_t* num_keep, int device);
+
+int b200det_batched_nms_host(
+    const void* boxes, const void* scores, const int64_t* idxs, int dtype,
+    int64_t N, double iou_threshold, int mode, int64_t* keep,
+    int64_t* num_keep, int device);
+
+void b200det_host_release(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_DETECTION_OPS_H */
