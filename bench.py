@@ -1,0 +1,481 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the roi_align / nms hot path (see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+
+One "step" = one MultiScaleRoIAlign forward + backward over one batch (BASELINE.json configs[2]:
+4 FPN levels of an 800x1088 image, batch 16 per GPU, 512 RoIs/img, 14x14 output, sampling_ratio 2,
+fp32, channels_last features) through the C-ABI library.  `value` = RoIs/s (fwd+bwd), whole job.
+Every rank works on its own 16 images (shard by image, no data-path collective) -> "weak" scaling.
+Inputs (1.18 GB features + 1.64 GB upstream gradient per rank) are far larger than the 126 MB L2, so
+no L2 flush is needed between iterations.
+
+Extra objects on the JSON line: roofline (dominant kernel vs the measured HBM peak), e2e (same step
+through the *_host C-ABI with pinned host buffers, copies inside the timed region), cpu_baseline
+(the reference's own CPU kernels, oracle/_ref, on a bounded sample), clocks, gpu_launches, and
+`secondary` (cfg1 roi_align, cfg3 bf16, cfg2 batched_nms boxes/s).
+
+--impl reference times the reference's CPU implementation (oracle/_ref/libtvref.so, all host
+threads) on a bounded sample of the same workload and prints the same line with impl=reference.
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+SHAPES = [(200, 272), (100, 136), (50, 68), (25, 34)]
+SCALES = [0.25, 0.125, 0.0625, 0.03125]
+IMAGE = (800, 1088)
+C = 256
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=30)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--workload", default="cfg3_fp32", choices=["cfg3_fp32", "cfg3_bf16"])
+    p.add_argument("--no-extras", action="store_true", help="skip e2e / cpu_baseline / secondary legs")
+    p.add_argument("--gather", action="store_true", help="also time the NCCL all-gather of pooled features")
+    return p.parse_args()
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# --------------------------------------------------------------------------------------- workload
+def make_rois(gen, batch, per_img, lo, hi, device):
+    """per_img boxes per image, sqrt(area) log-uniform in [lo, hi], clipped to the image, grouped by image."""
+    k = batch * per_img
+    h, w = IMAGE
+    u = lambda: torch.rand(k, generator=gen, device=device)
+    side = torch.exp(u() * (torch.log(torch.tensor(hi / lo))) + torch.log(torch.tensor(lo)))
+    aspect = torch.exp((u() - 0.5) * 1.0)
+    bw, bh = (side * aspect).clamp(max=w), (side / aspect).clamp(max=h)
+    cx, cy = u() * w, u() * h
+    x1, y1 = (cx - bw / 2).clamp(0, w - 2), (cy - bh / 2).clamp(0, h - 2)
+    x2, y2 = torch.maximum((cx + bw / 2).clamp(max=w), x1 + 1), torch.maximum((cy + bh / 2).clamp(max=h), y1 + 1)
+    b = torch.arange(batch, device=device).repeat_interleave(per_img).float()
+    return torch.stack([b, x1, y1, x2, y2], 1).contiguous()
+
+
+def make_cfg3(device, dtype, seed, batch=16, per_img=512, ph=14):
+    gen = torch.Generator(device=device).manual_seed(seed)
+    feats = [torch.randn(batch, C, h, w, generator=gen, device=device, dtype=torch.float32).to(dtype)
+             .contiguous(memory_format=torch.channels_last) for h, w in SHAPES]
+    rois = make_rois(gen, batch, per_img, 16.0, 800.0, device)
+    grad = torch.randn(batch * per_img, C, ph, ph, generator=gen, device=device, dtype=torch.float32).to(dtype) \
+        .contiguous(memory_format=torch.channels_last)
+    return feats, rois, grad
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons with NVML every 10 ms while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.ok, self._stop = [], set(), False, threading.Event()
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            self.nv, self.h = nv, nv.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # pragma: no cover
+            self.err = repr(e)
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                 "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def start(self):
+        if self.ok:
+            self.t.start()
+
+    def stop(self):
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"]}
+        self._stop.set()
+        self.t.join()
+        s = self.samples or [0]
+        return {"sm_mhz": statistics.median(s), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def physical_gpu_index(local):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local])
+        except Exception:
+            return local
+    return local
+
+
+# --------------------------------------------------------------------------------------- reference arm
+def cpu_reference_sample(feats_cpu, rois_cpu, grad_cpu, ph, stride, threads, repeats=1):
+    """The reference's CPU roi_align (oracle/_ref, unmodified kernels) on every `stride`-th RoI of the
+    workload, forward + backward, level by level like its Python MultiScaleRoIAlign does
+    (torchvision/ops/poolers.py:200-222).  Returns (seconds per pass, RoIs per pass, kind)."""
+    import oracle
+
+    kind = "reference" if oracle.have_ref() else "port"
+    impl = "ref" if kind == "reference" else "oracle"
+    sel = torch.arange(0, rois_cpu.shape[0], stride)
+    r = rois_cpu[sel].contiguous()
+    # grad_cpu is either the full [K,...] gradient or already the selected rows
+    g = (grad_cpu if grad_cpu.shape[0] == sel.numel() else grad_cpu[sel]).contiguous()
+    levels = oracle.fpn_level_map(r, 2, 5)
+    per_level = []
+    for l in range(4):
+        idx = torch.nonzero(levels == l).flatten()
+        per_level.append((r[idx].contiguous(), g[idx].contiguous()))
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        for l, (rl, gl) in enumerate(per_level):
+            n, c, h, w = feats_cpu[l].shape
+            oracle.roi_align_forward(feats_cpu[l], rl, ph, ph, SCALES[l], 2, False, impl=impl, threads=threads)
+            oracle.roi_align_backward(gl, rl, SCALES[l], ph, ph, n, c, h, w, 2, False, impl=impl, threads=threads)
+        best = min(best, time.perf_counter() - t0)
+    return best, int(sel.numel()), kind
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    dtype = torch.float32
+    gen = torch.Generator().manual_seed(1234 + 3)
+    batch, per_img, ph = 16, 512, 14
+    feats = [torch.randn(batch, C, h, w, generator=gen) for h, w in SHAPES]
+    rois = make_rois(gen, batch, per_img, 16.0, 800.0, "cpu")
+    stride = 8  # 1024 of the 8192 RoIs per step: a few seconds of CPU work per step
+    k_s = len(range(0, rois.shape[0], stride))
+    gsel = torch.randn(k_s, C, ph, ph, generator=gen)  # upstream gradient of the sampled RoIs only
+
+    times = []
+    for i in range(args.warmup + args.steps):
+        sec, n, kind = cpu_reference_sample(feats, rois, gsel, ph, stride, threads)
+        if i >= args.warmup:
+            times.append(sec)
+        if sum(times) > 240:  # keep the whole run within a few minutes
+            break
+    ms = 1e3 * sum(times) / len(times)
+    val = n / (ms / 1e3)
+    sample = f"{n} of {rois.shape[0]} RoIs (every {stride}th) of the cfg3 batch, fwd+bwd, 4 levels"
+    line = {
+        "impl": "reference", "metric": "roi_align_fwd_bwd_rois_per_s", "value": val, "unit": "RoIs/s",
+        "n_gpus": args.gpus, "steps": len(times), "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config("cfg3_fp32"),
+        "cpu_baseline": {"value": val, "unit": "RoIs/s", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": val, "unit": "RoIs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(name):
+    return {
+        "workload": f"{name}: MultiScaleRoIAlign fwd+bwd, 4 FPN levels of 800x1088 (200x272..25x34), C=256, "
+                    "batch 16 per GPU, 512 RoIs/img, 14x14 output, sampling_ratio 2, aligned False "
+                    "(BASELINE.json configs[2])",
+        "layout": "channels_last features / outputs / gradients",
+        "rois_per_step_per_gpu": 8192,
+        "sharding": "by image, 16 images per rank, no data-path collective",
+        "l2": "inputs (1.18 GB features + 1.64 GB grad per rank in fp32) exceed the 126 MB L2; no flush needed",
+    }
+
+
+# --------------------------------------------------------------------------------------- b200 arm
+def time_events(fn, steps, warmup, sync):
+    """Device time of `steps` calls of fn() in ms (CUDA events on the current stream)."""
+    for _ in range(warmup):
+        fn()
+    sync()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        fn()
+    b.record()
+    b.synchronize()
+    return a.elapsed_time(b)
+
+
+def run_b200(args, rank, world, local):
+    import torch.distributed as dist
+
+    from cpu_vision_b200 import capi
+
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dtype = torch.bfloat16 if args.workload == "cfg3_bf16" else torch.float32
+    es = 2 if dtype == torch.bfloat16 else 4
+    batch, per_img, ph = 16, 512, 14
+    feats, rois, grad = make_cfg3(dev, dtype, 1234 + 3 + rank, batch, per_img, ph)
+    K = rois.shape[0]
+    shapes = [(batch, C, h, w) for h, w in SHAPES]
+    out = torch.empty(K, C, ph, ph, device=dev, dtype=dtype).contiguous(memory_format=torch.channels_last)
+    levels = torch.empty(K, dtype=torch.int32, device=dev)
+    gfeats = [torch.empty_like(f) for f in feats]
+
+    def fwd():
+        capi.msroi_align_forward(feats, rois, SCALES, ph, ph, 2, False, out=out)
+
+    lv_holder = {}
+
+    def fwd_keep_levels():
+        _, lv = capi.msroi_align_forward(feats, rois, SCALES, ph, ph, 2, False, out=out)
+        lv_holder["lv"] = lv
+
+    fwd_keep_levels()
+    levels = lv_holder["lv"]
+
+    def bwd():
+        capi.msroi_align_backward(grad, rois, levels, SCALES, shapes, ph, ph, 2, False, layout=capi.NHWC, outs=gfeats)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        fwd()
+        bwd()
+    barrier()
+    sampler = ClockSampler(physical_gpu_index(local))
+    sampler.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 1)]
+    ev[0].record()
+    for i in range(args.steps):
+        fwd()
+        ev[2 * i + 1].record()
+        bwd()
+        ev[2 * i + 2].record()
+    torch.cuda.synchronize()
+    barrier()
+    clocks = sampler.stop()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    fwd_ms = sum(ev[2 * i].elapsed_time(ev[2 * i + 1]) for i in range(args.steps)) / args.steps
+    bwd_ms = sum(ev[2 * i + 1].elapsed_time(ev[2 * i + 2]) for i in range(args.steps)) / args.steps
+    if world > 1:
+        t = torch.tensor([total_ms, fwd_ms, bwd_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, fwd_ms, bwd_ms = t.tolist()
+    ms_per_step = total_ms / args.steps
+    value = world * K / (ms_per_step / 1e3)
+
+    feat_bytes = sum(n * c * h * w for n, c, h, w in shapes) * es
+    out_bytes = K * C * ph * ph * es
+    algo = {"fwd": feat_bytes + out_bytes + K * 20, "bwd": out_bytes + feat_bytes + K * 20}
+    peak, peak_src = measured_peak()
+    dom = "bwd" if bwd_ms >= fwd_ms else "fwd"
+    dom_ms = bwd_ms if dom == "bwd" else fwd_ms
+    achieved = algo[dom] / (dom_ms / 1e3) / 1e9
+    roofline = {
+        "bound": "hbm", "kernel": f"msroi_align_{dom}", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": algo[dom],
+        "fwd": {"ms": fwd_ms, "GBps": algo["fwd"] / (fwd_ms / 1e3) / 1e9, "frac": algo["fwd"] / (fwd_ms / 1e3) / 1e9 / peak},
+        "bwd": {"ms": bwd_ms, "GBps": algo["bwd"] / (bwd_ms / 1e3) / 1e9, "frac": algo["bwd"] / (bwd_ms / 1e3) / 1e9 / peak},
+        "fwd_bwd_frac": (algo["fwd"] + algo["bwd"]) / (ms_per_step / 1e3) / 1e9 / peak,
+    }
+    line = {
+        "metric": "roi_align_fwd_bwd_rois_per_s", "value": value, "unit": "RoIs/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if dtype == torch.bfloat16 else "f32",
+        "data": "synthetic", "config": workload_config(args.workload), "roofline": roofline, "clocks": clocks,
+        # kernels of ours per step: fpn_level_map + msroi forward + msroi backward (memsets not counted)
+        "gpu_launches": 3 * args.steps,
+    }
+    if not args.no_extras:
+        line["e2e"] = e2e_leg(capi, feats, rois, grad, levels, shapes, ph, dtype, local, world, K, dist)
+        if rank == 0 and world == 1:
+            line["cpu_baseline"] = cpu_leg(feats, rois, grad, ph)
+            line["secondary"] = secondary_legs(capi, dev, peak)
+        if world > 1 and args.gather:
+            line["allgather"] = gather_leg(out, world, dist)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def e2e_leg(capi, feats, rois, grad, levels, shapes, ph, dtype, local, world, K, dist):
+    """Same step through the host-buffer C-ABI: pinned host inputs, H2D + kernels + D2H all timed."""
+    hf = [f.cpu().contiguous(memory_format=torch.channels_last).pin_memory() for f in feats]
+    hr = rois.cpu().pin_memory()
+    hg = grad.cpu().contiguous(memory_format=torch.channels_last).pin_memory()
+    hout = torch.empty_like(hg).pin_memory()
+    hlv = torch.empty(K, dtype=torch.int32).pin_memory()
+    hgf = [torch.empty_like(f).pin_memory() for f in hf]
+    hf = [f.contiguous(memory_format=torch.channels_last) for f in hf]
+    steps, warm = 5, 2
+
+    def step():
+        capi.msroi_align_forward_host(hf, hr, SCALES, ph, ph, 2, False, device=local, out=hout, levels=hlv)
+        capi.msroi_align_backward_host(hg, hr, hlv, SCALES, shapes, ph, ph, 2, False, layout=capi.NHWC,
+                                       device=local, outs=hgf)
+
+    for _ in range(warm):
+        step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    sec = (time.perf_counter() - t0) / steps  # the host calls return only after the D2H copies completed
+    if world > 1:
+        t = torch.tensor([sec], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sec = t.item()
+    capi.host_release()
+    nb = lambda ts: sum(t.numel() * t.element_size() for t in ts)
+    return {"value": world * K / sec, "unit": "RoIs/s", "ms_per_step": sec * 1e3,
+            "h2d_bytes_per_step": nb(hf) + 2 * nb([hr]) + nb([hg]) + nb([hlv]),
+            "d2h_bytes_per_step": nb([hout]) + nb([hlv]) + nb(hgf), "steps": steps,
+            "api": "b200det_msroi_align_forward_host + b200det_msroi_align_backward_host (pinned host buffers)"}
+
+
+def cpu_leg(feats, rois, grad, ph):
+    threads = os.cpu_count() or 1
+    stride = 8
+    sel = torch.arange(0, rois.shape[0], stride, device=rois.device)
+    fc = [f.float().cpu().contiguous() for f in feats]
+    sec, n, kind = cpu_reference_sample(fc, rois.cpu(), grad[sel].float().cpu().contiguous(), ph, stride, threads,
+                                        repeats=2)
+    return {"value": n / sec, "unit": "RoIs/s", "cores": threads, "kind": kind, "seconds": sec,
+            "sample": f"{n} of {rois.shape[0]} RoIs (every {stride}th) of the same batch, fwd+bwd, best of 2; "
+                      "forward sharded over RoIs, backward over images (<=16 threads)"}
+
+
+def secondary_legs(capi, dev, peak):
+    """Other BASELINE.json configs, device-timed with an L2 flush between iterations where the
+    working set is smaller than L2."""
+    res = {}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    sync = torch.cuda.synchronize
+
+    def timed(fn, iters=20, flush_l2=True):
+        for _ in range(3):
+            fn()
+        sync()
+        tot = 0.0
+        for _ in range(iters):
+            if flush_l2:
+                flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+            tot += a.elapsed_time(b)
+        return tot / iters
+
+    # cfg1: single level 2x256x200x272, 1000 RoIs/img, 7x7, sr=2, aligned
+    gen = torch.Generator(device=dev).manual_seed(1234 + 1)
+    x = torch.randn(2, C, 200, 272, generator=gen, device=dev).contiguous(memory_format=torch.channels_last)
+    r = make_rois(gen, 2, 1000, 16.0, 512.0, dev)
+    g = torch.randn(2000, C, 7, 7, generator=gen, device=dev).contiguous(memory_format=torch.channels_last)
+    gi = torch.empty_like(x)
+    f_ms = timed(lambda: capi.roi_align_forward(x, r, 7, 7, 0.25, 2, True))
+    b_ms = timed(lambda: capi.roi_align_backward(g, r, 0.25, 7, 7, 2, C, 200, 272, 2, True, layout=capi.NHWC, out=gi))
+    fb = x.numel() * 4 + g.numel() * 4 + 2000 * 20
+    res["cfg1_roi_align_fp32"] = {
+        "fwd_ms": f_ms, "bwd_ms": b_ms, "fwd_rois_per_s": 2000 / (f_ms / 1e3),
+        "fwd_bwd_rois_per_s": 2000 / ((f_ms + b_ms) / 1e3), "fwd_frac_of_hbm": fb / (f_ms / 1e3) / 1e9 / peak,
+        "bwd_frac_of_hbm": fb / (b_ms / 1e3) / 1e9 / peak, "l2": "flushed between iterations"}
+    del x, g, gi
+    # cfg2: batched_nms 5000 boxes x 80 classes, IoU 0.5 (coordinate-trick branch on CUDA, boxes.py:72)
+    n = 5000
+    xy = torch.rand(n, 2, generator=gen, device=dev) * 1000
+    boxes = torch.cat([xy, xy + torch.rand(n, 2, generator=gen, device=dev) * 200 + 10], 1)
+    scores = (torch.randperm(n, generator=gen, device=dev).float() / n)
+    idxs = torch.randint(0, 80, (n,), generator=gen, device=dev)
+    ws = capi.NmsWorkspace(n, dev)
+    ms = timed(lambda: capi.batched_nms(boxes, scores, idxs, 0.5, capi.BNMS_AUTO, workspace=ws, sync=False),
+               flush_l2=False)
+    ms_sync = timed(lambda: capi.batched_nms(boxes, scores, idxs, 0.5, capi.BNMS_AUTO, workspace=ws, sync=True),
+                    flush_l2=False)
+    kept = capi.batched_nms(boxes, scores, idxs, 0.5, capi.BNMS_AUTO, workspace=ws).numel()
+    res["cfg2_batched_nms_5000x80"] = {
+        "ms": ms, "boxes_per_s": n / (ms / 1e3), "iou_pairs_per_s": n * (n - 1) / 2 / (ms / 1e3), "kept": kept,
+        "ms_with_count_readback": ms_sync,
+        "frac_of_bandwidth_bound": ((n * 20 + kept * 8) / (peak * 1e9)) / (ms / 1e3)}
+    ms = timed(lambda: capi.nms(boxes, scores, 0.5, workspace=ws, sync=False), flush_l2=False)
+    res["nms_5000"] = {"ms": ms, "boxes_per_s": n / (ms / 1e3)}
+    return res
+
+
+def gather_leg(out, world, dist):
+    """NCCL all-gather of the pooled features (the optional exchange step of SURVEY.md 8e)."""
+    full = torch.empty((world * out.shape[0],) + tuple(out.shape[1:]), dtype=out.dtype, device=out.device,
+                       memory_format=torch.channels_last)
+    for _ in range(2):
+        dist.all_gather_into_tensor(full, out)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(5):
+        dist.all_gather_into_tensor(full, out)
+    b.record()
+    b.synchronize()
+    ms = a.elapsed_time(b) / 5
+    t = torch.tensor([ms], device=out.device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = t.item()
+    recv = (world - 1) * out.numel() * out.element_size()
+    return {"ms": ms, "recv_GBps_per_gpu": recv / (ms / 1e3) / 1e9, "bytes_received_per_gpu": recv}
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback")
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    try:
+        run_b200(args, rank, world, local)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

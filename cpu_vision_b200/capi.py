@@ -24,7 +24,8 @@ SYMBOLS = [
     "b200det_version", "b200det_last_error", "b200det_roi_align_forward", "b200det_roi_align_backward",
     "b200det_fpn_level_map", "b200det_msroi_align_forward", "b200det_msroi_align_backward",
     "b200det_nms_workspace_bytes", "b200det_nms", "b200det_batched_nms", "b200det_roi_align_forward_host",
-    "b200det_roi_align_backward_host", "b200det_nms_host", "b200det_batched_nms_host", "b200det_host_release",
+    "b200det_roi_align_backward_host", "b200det_msroi_align_forward_host", "b200det_msroi_align_backward_host",
+    "b200det_nms_host", "b200det_batched_nms_host", "b200det_host_release",
 ]
 
 _declared = False
@@ -50,6 +51,10 @@ def lib():
         l.b200det_roi_align_forward_host.argtypes = [_P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I, _I, _I]
         l.b200det_roi_align_backward_host.argtypes = [_P, _P, _L, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I,
                                                       _I, _I]
+        l.b200det_msroi_align_forward_host.argtypes = [_P, _P, _P, _P, _I, _I, _P, _P, _P, _I, _I, _L, _L, _L, _L, _L,
+                                                       _I, _I, _I, _I, _I, _I, _D, _I]
+        l.b200det_msroi_align_backward_host.argtypes = [_P, _P, _L, _P, _P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L,
+                                                        _L, _L, _I, _I, _I]
         l.b200det_nms_host.argtypes = [_P, _P, _I, _L, _D, _P, _P, _I]
         l.b200det_batched_nms_host.argtypes = [_P, _P, _P, _I, _L, _D, _I, _P, _P, _I]
         l.b200det_host_release.restype = None
@@ -259,6 +264,48 @@ def roi_align_backward_host(grad, rois, spatial_scale, pooled_h, pooled_w, N, Cc
                                                  int(device)),
            "b200det_roi_align_backward_host")
     return gi
+
+
+def _span(t):
+    return 1 + sum((s - 1) * st for s, st in zip(t.shape, t.stride())) if t.numel() else 0
+
+
+def msroi_align_forward_host(feats, rois, scales, pooled_h, pooled_w, sampling_ratio, aligned=False, k_min=2, k_max=5,
+                             canonical_scale=224, canonical_level=4, eps=1e-6, device=0, out=None, levels=None):
+    """CPU tensors in, CPU tensors out: (output, levels int32)."""
+    layout, f0 = _layout_of(feats[0])
+    mf = torch.channels_last if layout == NHWC else torch.contiguous_format
+    feats = [f.contiguous(memory_format=mf) for f in feats]
+    r = _arith(rois, f0.dtype)
+    N, Cc = f0.shape[:2]
+    K = r.shape[0]
+    if out is None:
+        out = _empty_like_layout((K, Cc, pooled_h, pooled_w), f0, layout)
+    if levels is None:
+        levels = torch.empty(K, dtype=torch.int32)
+    ptrs, hs, ws, sc = _level_arrays(feats, scales)
+    _check(lib().b200det_msroi_align_forward_host(ptrs, hs, ws, sc, len(feats), layout, r.data_ptr(),
+                                                  levels.data_ptr(), out.data_ptr(), layout, _dt(f0), N, Cc, K,
+                                                  pooled_h, pooled_w, int(sampling_ratio), int(bool(aligned)), k_min,
+                                                  k_max, canonical_scale, canonical_level, float(eps), int(device)),
+           "b200det_msroi_align_forward_host")
+    return out, levels
+
+
+def msroi_align_backward_host(grad, rois, levels, scales, shapes, pooled_h, pooled_w, sampling_ratio, aligned=False,
+                              layout=NCHW, device=0, outs=None):
+    r = _arith(rois, grad.dtype)
+    if outs is None:
+        outs = [_empty_like_layout(tuple(s), grad, layout) for s in shapes]
+    ptrs, hs, ws, sc = _level_arrays(outs, scales)
+    N, Cc = shapes[0][:2]
+    lv = levels.to(torch.int32).contiguous()
+    _check(lib().b200det_msroi_align_backward_host(grad.data_ptr(), _strides(grad), _span(grad), r.data_ptr(),
+                                                   lv.data_ptr(), ptrs, hs, ws, sc, len(outs), layout, _dt(grad), N,
+                                                   Cc, r.shape[0], pooled_h, pooled_w, int(sampling_ratio),
+                                                   int(bool(aligned)), int(device)),
+           "b200det_msroi_align_backward_host")
+    return outs
 
 
 def nms_host(boxes, scores, iou_threshold, device=0):

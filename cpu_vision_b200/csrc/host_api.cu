@@ -5,6 +5,7 @@
 // runs the device entry points of c_api.cu on a private stream and copies the
 // results back before returning.  Pinned caller buffers get full PCIe rate;
 // pageable ones work at whatever cudaMemcpyAsync's internal staging gives.
+#include <cstring>
 #include <mutex>
 
 #include "common.cuh"
@@ -119,6 +120,106 @@ int b200det_roi_align_backward_host(const void* grad, const int64_t* grad_stride
                                   PH, PW, spatial_scale, sampling_ratio, aligned, 1, st);
   if (rc) return rc;
   if (gi_b) B200DET_CUDA_OK(cudaMemcpyAsync(grad_input, d_gi, gi_b, cudaMemcpyDeviceToHost, st));
+  B200DET_CUDA_OK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+// byte offsets of every level inside one arena slot (256-byte aligned)
+static size_t level_offsets(const int64_t* heights, const int64_t* widths, int L, int64_t N,
+                            int64_t C, size_t es, size_t* off) {
+  size_t total = 0;
+  for (int l = 0; l < L; ++l) {
+    off[l] = total;
+    total += ((size_t)N * C * heights[l] * widths[l] * es + 255) & ~(size_t)255;
+  }
+  return total;
+}
+
+int b200det_msroi_align_forward_host(const void* const* feats, const int64_t* heights,
+                                     const int64_t* widths, const double* scales, int num_levels,
+                                     int layout, const void* rois, int32_t* levels, void* output,
+                                     int out_layout, int dtype, int64_t N, int64_t C, int64_t K,
+                                     int64_t PH, int64_t PW, int sampling_ratio, int aligned,
+                                     int k_min, int k_max, int canonical_scale,
+                                     int canonical_level, double eps, int device) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  const size_t es = dtype_size(dtype);
+  if (!es) return fail(B200DET_ENOSUP, "msroi_align_forward_host: unknown dtype %d", dtype);
+  if (num_levels < 1 || num_levels > B200DET_MAX_LEVELS || !feats || !heights || !widths || !scales)
+    return fail(B200DET_EINVAL, "msroi_align_forward_host: bad level description");
+  if (N < 0 || C < 0 || K < 0 || PH < 0 || PW < 0)
+    return fail(B200DET_EINVAL, "msroi_align_forward_host: negative size");
+  int rc = arena_bind(device);
+  if (rc) return rc;
+  size_t off[B200DET_MAX_LEVELS];
+  const size_t feat_b = level_offsets(heights, widths, num_levels, N, C, es, off);
+  const size_t roi_b = (size_t)K * 5 * (dtype == B200DET_F64 ? 8 : 4),
+               out_b = (size_t)K * C * PH * PW * es;
+  void *d_feat, *d_roi, *d_out, *d_lv;
+  if ((rc = arena_get(0, feat_b, &d_feat)) || (rc = arena_get(1, roi_b, &d_roi)) ||
+      (rc = arena_get(2, out_b, &d_out)) || (rc = arena_get(3, (size_t)K * 4, &d_lv)))
+    return rc;
+  cudaStream_t st = g_arena.stream;
+  const void* d_ptrs[B200DET_MAX_LEVELS];
+  if (roi_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_roi, rois, roi_b, cudaMemcpyHostToDevice, st));
+  for (int l = 0; l < num_levels; ++l) {
+    d_ptrs[l] = (char*)d_feat + off[l];
+    const size_t b = (size_t)N * C * heights[l] * widths[l] * es;
+    if (b) B200DET_CUDA_OK(cudaMemcpyAsync((void*)d_ptrs[l], feats[l], b, cudaMemcpyHostToDevice, st));
+  }
+  rc = b200det_msroi_align_forward(d_ptrs, heights, widths, scales, num_levels, layout, d_roi,
+                                   (int32_t*)d_lv, 0, d_out, out_layout, dtype, N, C, K, PH, PW,
+                                   sampling_ratio, aligned, k_min, k_max, canonical_scale,
+                                   canonical_level, eps, st);
+  if (rc) return rc;
+  if (out_b) B200DET_CUDA_OK(cudaMemcpyAsync(output, d_out, out_b, cudaMemcpyDeviceToHost, st));
+  if (levels && K && num_levels > 1)
+    B200DET_CUDA_OK(cudaMemcpyAsync(levels, d_lv, (size_t)K * 4, cudaMemcpyDeviceToHost, st));
+  B200DET_CUDA_OK(cudaStreamSynchronize(st));
+  if (levels && num_levels == 1) memset(levels, 0, (size_t)K * 4);
+  return 0;
+}
+
+int b200det_msroi_align_backward_host(const void* grad, const int64_t* grad_strides,
+                                      int64_t grad_span_elems, const void* rois,
+                                      const int32_t* levels, void* const* grad_feats,
+                                      const int64_t* heights, const int64_t* widths,
+                                      const double* scales, int num_levels, int layout, int dtype,
+                                      int64_t N, int64_t C, int64_t K, int64_t PH, int64_t PW,
+                                      int sampling_ratio, int aligned, int device) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  const size_t es = dtype_size(dtype);
+  if (!es) return fail(B200DET_ENOSUP, "msroi_align_backward_host: unknown dtype %d", dtype);
+  if (num_levels < 1 || num_levels > B200DET_MAX_LEVELS || !grad_feats || !heights || !widths || !scales)
+    return fail(B200DET_EINVAL, "msroi_align_backward_host: bad level description");
+  if (N < 0 || C < 0 || K < 0 || PH < 0 || PW < 0 || grad_span_elems < 0)
+    return fail(B200DET_EINVAL, "msroi_align_backward_host: negative size");
+  if (num_levels > 1 && K > 0 && !levels)
+    return fail(B200DET_EINVAL, "msroi_align_backward_host: levels required");
+  int rc = arena_bind(device);
+  if (rc) return rc;
+  size_t off[B200DET_MAX_LEVELS];
+  const size_t feat_b = level_offsets(heights, widths, num_levels, N, C, es, off);
+  const size_t roi_b = (size_t)K * 5 * (dtype == B200DET_F64 ? 8 : 4),
+               g_b = (size_t)grad_span_elems * es;
+  void *d_feat, *d_roi, *d_g, *d_lv;
+  if ((rc = arena_get(0, feat_b, &d_feat)) || (rc = arena_get(1, roi_b, &d_roi)) ||
+      (rc = arena_get(2, g_b, &d_g)) || (rc = arena_get(3, (size_t)K * 4, &d_lv)))
+    return rc;
+  cudaStream_t st = g_arena.stream;
+  void* d_ptrs[B200DET_MAX_LEVELS];
+  for (int l = 0; l < num_levels; ++l) d_ptrs[l] = (char*)d_feat + off[l];
+  if (roi_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_roi, rois, roi_b, cudaMemcpyHostToDevice, st));
+  if (levels && K) B200DET_CUDA_OK(cudaMemcpyAsync(d_lv, levels, (size_t)K * 4, cudaMemcpyHostToDevice, st));
+  if (g_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_g, grad, g_b, cudaMemcpyHostToDevice, st));
+  rc = b200det_msroi_align_backward(d_g, grad_strides, d_roi, (const int32_t*)d_lv, d_ptrs, heights,
+                                    widths, scales, num_levels, layout, dtype, N, C, K, PH, PW,
+                                    sampling_ratio, aligned, 1, st);
+  if (rc) return rc;
+  for (int l = 0; l < num_levels; ++l) {
+    const size_t b = (size_t)N * C * heights[l] * widths[l] * es;
+    if (b) B200DET_CUDA_OK(cudaMemcpyAsync(grad_feats[l], d_ptrs[l], b, cudaMemcpyDeviceToHost, st));
+  }
   B200DET_CUDA_OK(cudaStreamSynchronize(st));
   return 0;
 }

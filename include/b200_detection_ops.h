@@ -194,6 +194,24 @@ int b200det_roi_align_backward_host(
     int64_t C, int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
     double spatial_scale, int sampling_ratio, int aligned, int device);
 
+/* Host-buffer MultiScaleRoIAlign (forward, backward): feats[l] / grad_feats[l],
+ * rois, levels, output and grad are HOST pointers with the same meaning as in
+ * the device entry points above.  `levels` may be NULL in the forward. */
+int b200det_msroi_align_forward_host(
+    const void* const* feats, const int64_t* heights, const int64_t* widths,
+    const double* scales, int num_levels, int layout, const void* rois,
+    int32_t* levels, void* output, int out_layout, int dtype, int64_t N,
+    int64_t C, int64_t K, int64_t PH, int64_t PW, int sampling_ratio,
+    int aligned, int k_min, int k_max, int canonical_scale,
+    int canonical_level, double eps, int device);
+
+int b200det_msroi_align_backward_host(
+    const void* grad, const int64_t* grad_strides, int64_t grad_span_elems,
+    const void* rois, const int32_t* levels, void* const* grad_feats,
+    const int64_t* heights, const int64_t* widths, const double* scales,
+    int num_levels, int layout, int dtype, int64_t N, int64_t C, int64_t K,
+    int64_t PH, int64_t PW, int sampling_ratio, int aligned, int device);
+
 int b200det_nms_host(
     const void* boxes, const void* scores, int dtype, int64_t N,
     double iou_threshold, int64_t* keep, int64_t* num_keep, int device);

@@ -1,0 +1,193 @@
+"""Parity of the device NMS / batched NMS with the oracle: keep indices must be
+bit-exact (torch.equal), through the C-ABI, the host-buffer C-ABI and the
+dispatcher.  Mirrors the reference's TestNMS (test/test_ops.py:744-918)."""
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from cpu_vision_b200 import capi as c
+
+    return c
+
+
+def make_boxes(g, n, span=1000.0, lo=10.0, hi=210.0, distinct=True):
+    xy = torch.rand(n, 2, generator=g) * span
+    wh = torch.rand(n, 2, generator=g) * (hi - lo) + lo
+    scores = torch.randperm(n, generator=g).float() / n if distinct else torch.rand(n, generator=g)
+    return torch.cat([xy, xy + wh], 1), scores
+
+
+def test_golden(golden, capi):
+    d = golden("nms.pt")
+    b, s = d["boxes"].to(DEV), d["scores"].to(DEV)
+    for thr in (0.2, 0.5, 0.7):
+        assert torch.equal(capi.nms(b, s, thr).cpu(), d[f"keep_{thr}"])
+    assert torch.equal(capi.nms(b, d["scores_ties"].to(DEV), 0.5).cpu(), d["keep_ties"]), "stable tie order"
+    i = d["idxs"].to(DEV)
+    assert torch.equal(capi.batched_nms(b, s, i, 0.5, capi.BNMS_TRICK).cpu(), d["bn_trick"])
+    assert torch.equal(capi.batched_nms(b, s, i, 0.5, capi.BNMS_VANILLA).cpu(), d["bn_vanilla"])
+    b2, s2, i2 = d["boxes2"].to(DEV), d["scores2"].to(DEV), d["idxs2"].to(DEV)
+    assert torch.equal(capi.batched_nms(b2, s2, i2, 0.5, capi.BNMS_TRICK).cpu(), d["bn2_trick"])
+    assert torch.equal(capi.batched_nms(b2, s2, i2, 0.5, capi.BNMS_VANILLA).cpu(), d["bn2_vanilla"])
+    k = golden("known_answers.pt")
+    assert capi.nms(k["K1_boxes"].to(DEV), k["K1_scores"].to(DEV), 0.2).tolist() == [1]
+    assert capi.nms(k["K1_boxes"].half().to(DEV), k["K1_scores"].half().to(DEV), 0.2).tolist() == [1]  # test_nms_float16
+
+
+@pytest.mark.parametrize("n", [1, 2, 63, 64, 65, 127, 128, 129, 1000, 5000])
+@pytest.mark.parametrize("thr", [0.2, 0.5, 0.8])
+def test_random_vs_oracle(capi, n, thr):
+    for seed in range(3):
+        g = torch.Generator().manual_seed(1000 * seed + n)
+        b, s = make_boxes(g, n, span=300.0 if n >= 1000 else 100.0)
+        want = oracle.nms(b, s, thr)
+        got = capi.nms(b.to(DEV), s.to(DEV), thr)
+        assert torch.equal(got.cpu(), want), (n, thr, seed)
+
+
+def test_reference_style_engineered_overlap(capi):
+    """test_ops.py:769-795: one box engineered to sit just above the threshold."""
+    for thr in (0.2, 0.5, 0.8):
+        g = torch.Generator().manual_seed(int(thr * 100))
+        n = 1000
+        b = torch.rand(n, 4, generator=g) * 100
+        b[:, 2:] += b[:, :2]
+        b[-1, :] = b[0, :]
+        x0, y0, x1, y1 = b[-1].tolist()
+        b[-1, 2] += (x1 - x0) * (1 - thr) / thr - 1e-5
+        s = torch.rand(n, generator=g)
+        assert torch.equal(capi.nms(b.to(DEV), s.to(DEV), thr).cpu(), oracle.nms(b, s, thr))
+
+
+def test_ties_nan_free_duplicates(capi):
+    g = torch.Generator().manual_seed(3)
+    b, _ = make_boxes(g, 500, span=80.0)
+    b = torch.cat([b, b[:100]])                                   # exact duplicates
+    s = torch.cat([torch.full((300,), 0.5), torch.rand(300, generator=g)])  # long tie run
+    assert torch.equal(capi.nms(b.to(DEV), s.to(DEV), 0.5).cpu(), oracle.nms(b, s, 0.5))
+    z = torch.zeros(10, 4)                                        # degenerate zero-area boxes: 0/0 -> NaN > thr false
+    assert torch.equal(capi.nms(z.to(DEV), torch.arange(10.0).to(DEV), 0.5).cpu(), oracle.nms(z, torch.arange(10.0), 0.5))
+
+
+def test_fp64_and_empty(capi):
+    g = torch.Generator().manual_seed(8)
+    b, s = make_boxes(g, 700, span=150.0)
+    b, s = b.double(), s.double()
+    assert torch.equal(capi.nms(b.to(DEV), s.to(DEV), 0.5).cpu(), oracle.nms(b, s, 0.5))
+    e = capi.nms(torch.zeros(0, 4, device=DEV), torch.zeros(0, device=DEV), 0.5)
+    assert e.shape == (0,) and e.dtype == torch.int64
+
+
+@pytest.mark.parametrize("n,classes", [(1000, 4), (5000, 80), (3000, 1), (5001, 90)])
+def test_batched_vs_oracle(capi, n, classes):
+    """cfg2: 5000 boxes x 80 classes, IoU 0.5 -> bit-exact keep indices (both strategies and AUTO)."""
+    for seed in range(2):
+        g = torch.Generator().manual_seed(1234 + 2 + seed)
+        b, s = make_boxes(g, n)
+        idx = torch.randint(0, classes, (n,), generator=g)
+        bd, sd, idd = b.to(DEV), s.to(DEV), idx.to(DEV)
+        assert torch.equal(capi.batched_nms(bd, sd, idd, 0.5, capi.BNMS_TRICK).cpu(),
+                           oracle.batched_nms(b, s, idx, 0.5, "trick"))
+        assert torch.equal(capi.batched_nms(bd, sd, idd, 0.5, capi.BNMS_VANILLA).cpu(),
+                           oracle.batched_nms(b, s, idx, 0.5, "vanilla"))
+        assert torch.equal(capi.batched_nms(bd, sd, idd, 0.5, capi.BNMS_AUTO).cpu(),
+                           oracle.batched_nms(b, s, idx, 0.5, "auto_cuda"))
+
+
+def test_batched_nms_implementations_agree(capi):
+    """test_ops.py:894-918: vanilla == coordinate trick for N=1000, 4 classes, thr 0.9; empty input."""
+    for seed in range(5):
+        g = torch.Generator().manual_seed(seed)
+        b = torch.rand(1000, 4, generator=g) * 100
+        b[:, 2:] += b[:, :2]
+        s = torch.randperm(1000, generator=g).float() / 1000
+        idx = torch.randint(0, 4, (1000,), generator=g)
+        a = capi.batched_nms(b.to(DEV), s.to(DEV), idx.to(DEV), 0.9, capi.BNMS_TRICK)
+        c = capi.batched_nms(b.to(DEV), s.to(DEV), idx.to(DEV), 0.9, capi.BNMS_VANILLA)
+        assert torch.equal(a, c)
+    import cpu_vision_b200 as m
+
+    e = m.batched_nms(torch.zeros(0, 4, device=DEV), torch.zeros(0, device=DEV), torch.zeros(0, dtype=torch.int64, device=DEV), 0.2)
+    assert e.numel() == 0 and e.dtype == torch.int64
+
+
+def test_host_buffer_entry_points(capi):
+    g = torch.Generator().manual_seed(21)
+    b, s = make_boxes(g, 2000, span=300.0)
+    idx = torch.randint(0, 20, (2000,), generator=g)
+    assert torch.equal(capi.nms_host(b.pin_memory(), s.pin_memory(), 0.5), oracle.nms(b, s, 0.5))
+    assert torch.equal(capi.batched_nms_host(b, s, idx, 0.5), oracle.batched_nms(b, s, idx, 0.5, "auto_cuda"))
+    x = torch.randn(2, 64, 30, 40, generator=g)
+    rois = torch.tensor([[0, 4.0, 4, 60, 50], [1, 10, 20, 100, 110], [1, 0, 0, 159, 119]])
+    out = capi.roi_align_forward_host(x, rois, 7, 7, 0.25, 2, True)
+    torch.testing.assert_close(out, oracle.roi_align_forward(x, rois, 7, 7, 0.25, 2, True), rtol=1e-5, atol=1e-6)
+    go = torch.randn(3, 64, 7, 7, generator=g)
+    gi = capi.roi_align_backward_host(go, rois, 0.25, 7, 7, 2, 64, 30, 40, 2, True)
+    torch.testing.assert_close(gi, oracle.roi_align_backward(go, rois, 0.25, 7, 7, 2, 64, 30, 40, 2, True),
+                               rtol=1e-4, atol=1e-5)
+    capi.host_release()
+
+
+def test_dispatcher_nms_and_errors():
+    import cpu_vision_b200 as m
+
+    g = torch.Generator().manual_seed(33)
+    b, s = make_boxes(g, 1500, span=200.0)
+    assert torch.equal(torch.ops.torchvision.nms(b.to(DEV), s.to(DEV), 0.5).cpu(), oracle.nms(b, s, 0.5))
+    assert torch.equal(m.nms(b.to(DEV), s.to(DEV), 0.7).cpu(), oracle.nms(b, s, 0.7))
+    idx = torch.randint(0, 80, (1500,), generator=g)
+    assert torch.equal(m.batched_nms(b.to(DEV), s.to(DEV), idx.to(DEV), 0.5).cpu(),
+                       oracle.batched_nms(b, s, idx, 0.5, "auto_cuda"))
+    # test_ops.py:797-805 input errors
+    with pytest.raises(RuntimeError):
+        m.nms(torch.rand(4, device=DEV), torch.rand(3, device=DEV), 0.5)
+    with pytest.raises(RuntimeError):
+        m.nms(torch.rand(3, 5, device=DEV), torch.rand(5, device=DEV), 0.5)
+    with pytest.raises(RuntimeError):
+        m.nms(torch.rand(3, 4, device=DEV), torch.rand(3, 2, device=DEV), 0.5)
+    with pytest.raises(RuntimeError):
+        m.nms(torch.rand(3, 4, device=DEV), torch.rand(4, device=DEV), 0.5)
+
+
+def test_full_size_properties(capi):
+    """cfg2 'reading B' scale: properties that hold at any N (no oracle needed):
+    no two kept boxes of a class overlap above thr; every dropped box is covered by
+    a kept higher-scored box of its class; nms of the kept set keeps everything."""
+    g = torch.Generator().manual_seed(77)
+    n, classes, thr = 20000, 80, 0.5
+    b, s = make_boxes(g, n, span=2000.0)
+    idx = torch.randint(0, classes, (n,), generator=g)
+    bd, sd, idd = b.to(DEV), s.to(DEV), idx.to(DEV)
+    keep = capi.batched_nms(bd, sd, idd, thr, capi.BNMS_VANILLA)
+    assert torch.all(sd[keep][:-1] >= sd[keep][1:]), "descending score order"
+    kb, kc, ks = bd[keep].double(), idd[keep], sd[keep]
+
+    def iou(a, c):
+        lt = torch.maximum(a[:, None, :2], c[None, :, :2])
+        rb = torch.minimum(a[:, None, 2:], c[None, :, 2:])
+        wh = (rb - lt).clamp(min=0)
+        inter = wh[..., 0] * wh[..., 1]
+        aa = (a[:, 2] - a[:, 0]) * (a[:, 3] - a[:, 1])
+        ac = (c[:, 2] - c[:, 0]) * (c[:, 3] - c[:, 1])
+        return inter / (aa[:, None] + ac[None, :] - inter)
+
+    m = iou(kb, kb)
+    same = kc[:, None] == kc[None, :]
+    m = torch.where(same, m, torch.zeros_like(m))
+    m.fill_diagonal_(0)
+    assert (m > thr + 1e-6).sum().item() == 0
+    dropped = torch.ones(n, dtype=torch.bool, device=DEV)
+    dropped[keep] = False
+    di = torch.nonzero(dropped).flatten()
+    cover = iou(bd[di].double(), kb)
+    ok = (cover > thr - 1e-6) & (idd[di][:, None] == kc[None, :]) & (ks[None, :] > sd[di][:, None])
+    assert ok.any(dim=1).all()
+    again = capi.batched_nms(bd[keep], sd[keep], idd[keep], thr, capi.BNMS_VANILLA)
+    assert torch.equal(again, torch.arange(keep.numel(), device=DEV))
