@@ -1,6 +1,6 @@
 // c_api.cu -- extern "C" entry points declared in include/b200_detection_ops.h.
 // Argument validation, layout bookkeeping and kernel selection live here; the
-// kernels are in roi_align_fast.cu / roi_align_generic.cu / nms_sm100.cu.
+// kernels are in roi_align_sm100.cu / roi_align_generic.cu / nms_sm100.cu.
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>

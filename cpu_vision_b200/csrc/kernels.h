@@ -31,7 +31,7 @@ int roi_align_bwd_generic(const LevelArgs& lv, int dtype, const void* grad, cons
 int fpn_level_map(const void* rois, int dtype, long long K, int k_min, int k_max, int s0, int lvl0,
                   double eps, int32_t* levels, cudaStream_t st);
 
-// roi_align_fast.cu: returns 1 when it took the call, 0 when the generic path
+// roi_align_sm100.cu: returns 1 when it took the call, 0 when the generic path
 // must run, <0 / >0 on error like the public API.
 int roi_align_fwd_fast(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
                        void* out, int out_layout, long long K, int PH, int PW, int sr,

@@ -144,8 +144,11 @@ def test_forward_backward_16bit(capi, dtype, rtol, atol, btol, channels_last, ph
                                  layout=capi.NHWC if channels_last else capi.NCHW)
     assert gi.dtype == dtype
     # packed 16-bit red.global.add rounds after EVERY accumulation (the reference under autocast
-    # accumulates in fp32 and rounds once): n contributions cost up to ~sqrt(n) * 2^-9 (bf16) / 2^-11 (fp16)
-    close_bwd(gi, want64, rtol=btol)
+    # accumulates in fp32 and rounds once): n contributions cost up to ~sqrt(n) * 2^-9 (bf16) / 2^-11 (fp16).
+    # The NCHW fallback kernel issues one 16-bit atomic per sample tap (16 per output element, in a
+    # run-dependent order) where the channels_last kernel sums a whole column in fp32 first, so its
+    # rounding error is larger and varies from run to run: twice the bound there.
+    close_bwd(gi, want64, rtol=btol if channels_last else 2 * btol)
 
 
 def test_fp64_matches_oracle(capi):
