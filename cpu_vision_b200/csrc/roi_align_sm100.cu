@@ -519,8 +519,9 @@ bool eligible(const LevelArgs& lv, int dtype, int PH, int PW, int sr) {
   return true;
 }
 
-// How many RoIs ahead the forward prefetches into L2: about two generations of
-// resident CTAs (148 SMs x 3 CTAs / CT tiles).  B200DET_PF_DIST overrides (0 = off).
+// How many RoIs ahead the forward prefetches into L2.  Measured on B200 (kbench, r01): the
+// prefetch LOSES (cfg3 fp32 fwd 0.70 ms off vs 0.78 ms at the old default, cfg1 0.09 vs 0.24 ms),
+// so it is off unless B200DET_PF_DIST=<RoIs ahead> asks for it.
 int prefetch_distance(int CT) {
   static int env = -2;
   if (env == -2) {
@@ -528,7 +529,8 @@ int prefetch_distance(int CT) {
     env = s ? atoi(s) : -1;
   }
   if (env >= 0) return env;
-  return 2 * 148 * 3 / (CT > 0 ? CT : 1);
+  (void)CT;
+  return 0;
 }
 
 template <typename T>
