@@ -1,48 +1,18 @@
-// roi_align_sm100.cu -- the sm_100a RoIAlign kernels for the detection-model
-// case: channels_last feature maps, C a multiple of 128, sampling_ratio 1 or 2,
-// pooled_width * sampling_ratio <= 32.  Everything else goes to
-// roi_align_generic.cu.
+// roi_align_sm100.cu -- the sm_100a RoIAlign BACKWARD kernel for the detection-model
+// case (channels_last, C % 128 == 0, sampling_ratio 1 or 2, pooled_width *
+// sampling_ratio <= 32); the forward lives in roi_align_fwd_sm100.cu, everything
+// else in roi_align_generic.cu.
 //
-// bilinear_interpolate (cuda/roi_align_kernel.cu:14-66) is separable: the
-// weight of pixel (r, c) for a sample is wy(r) * wx(c).  Summed over the
-// sampling grid of a bin that gives, for a pooled row ph,
-//     out[ph][pw] = sum_c Wx[pw][c] * ( sum_r Wy[ph][r] * in[r][c] ).
-//
-// FORWARD.  CTA = one (RoI, 128-channel tile), 7 warps; a warp takes one pooled
-// row at a time; a lane owns 4 consecutive channels, so every feature tap is one
-// 16-byte (fp32) / 8-byte (bf16, fp16) load and a warp covers 512/256 contiguous
-// bytes of one NHWC pixel.
-//   * Warp 0 builds the x table once per CTA (it is the same for every pooled
-//     row): per x sample its two tap weights and how many NEW feature columns
-//     the sample needs (0, 1 or 2), plus the ordered list of those columns
-//     ("column events").  It also prefetches into L2, with
-//     cp.async.bulk.prefetch.L2, the footprint rows of a RoI a few hundred CTAs
-//     ahead, so first-touch HBM latency is not paid by demand loads.
-//   * Each warp derives the <= 2*SR feature rows of its pooled row with their
-//     merged weights (1/count folded in; exact, count is a power of two).
-//   * It then sweeps the x samples left to right keeping the vertical sums of
-//     the two columns under the current sample in registers.  Each (row,
-//     column) of the footprint is loaded once per pooled row; the loads of column
-//     event e+1 are issued before the FMAs of event e (two register buffers).
-//   * fp32 math is issued as packed FFMA2 (fma.rn.f32x2, new on sm_100): half
-//     the FMA instructions of a scalar formulation, same rounding.
-//
-// BACKWARD is the transpose with a warp per PAIR of pooled rows (fewer atomics:
-// the rows two adjacent pooled rows share are reduced once): per column it
-// accumulates sum_pw Wx[pw][c] * grad[ph][pw] in registers and issues ONE vector
-// red.global.add per (row, column) of the footprint (4 channels per lane, 128
-// channels per warp instruction) instead of 4 scalar atomics per sample.
-#include <stdlib.h>
-
-#include "common.cuh"
-#include "kernels.h"
+// The backward is the transpose of the separable forward with a warp per PAIR of
+// pooled rows (fewer atomics: the rows two adjacent pooled rows share are reduced
+// once): per column it accumulates sum_pw Wx[pw][c] * grad[ph][pw] in registers and
+// issues ONE vector red.global.add per (row, column) of the footprint (4 channels
+// per lane, 128 channels per warp instruction) instead of 4 scalar atomics per
+// sample (cuda/roi_align_kernel.cu:303-327).
+#include "sm100_common.cuh"
 
 namespace b200det {
 namespace {
-
-constexpr int kFwdWarps = 7;
-constexpr int kMaxSX = 32;  // x samples per pooled row handled by one warp
-constexpr unsigned kFull = 0xffffffffu;
 
 // ---- 4-channel vector I/O ---------------------------------------------------
 template <typename T> struct V4;
@@ -116,218 +86,6 @@ __device__ __forceinline__ void fma4(float4& a, float w, const float4& v) {
   asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(a1) : "l"(ww), "l"(v1));
   asm("mov.b64 {%0, %1}, %2;" : "=f"(a.x), "=f"(a.y) : "l"(a0));
   asm("mov.b64 {%0, %1}, %2;" : "=f"(a.z), "=f"(a.w) : "l"(a1));
-}
-
-// ---- x table (one warp, once per CTA) ------------------------------------------
-// Lane j owns x sample j (pooled column j / SR, sample j % SR).  The sweep keeps
-// a window of two feature columns (lo, hi = lo + 1, clamped like
-// roi_align_kernel.cu:34-46).  A sample reaches its taps by leaving the window
-// unchanged, sliding it right by one column (one new column) or reloading both.
-struct XTable {
-  float2 w[kMaxSX];        // (hx, lx): weights of the lo / hi column; 0 for an empty sample
-  int colofs[2 * kMaxSX];  // element offsets (x * C) of the column events, in sweep order
-  unsigned m_slide;        // bit j: sample j slides the window (1 new column)
-  unsigned m_reload;       // bit j: sample j reloads the window (2 new columns)
-  unsigned m_valid;        // bit j: sample j is not empty (roi_align_kernel.cu:23-26)
-  int ncol;
-};
-
-template <int SR>
-__device__ __forceinline__ void build_xtable(const RoiGeom<float>& g, int W, int C, int PW, int lane, XTable& xt) {
-  const int SX = PW * SR;
-  const int j = lane < SX ? lane : SX - 1;
-  const float x = sample_coord<float>(g.start_w, g.bin_w, j / SR, j % SR, SR);
-  const AxisTap<float> t = axis_tap<float>(x, W);
-  // an empty sample parks the window at the edge it fell off (its weights are zero)
-  const int xl = t.valid ? t.lo : (x < -1.0f ? 0 : W - 1);
-  const int xh = min(xl + 1, W - 1);
-  int pxl = __shfl_up_sync(kFull, xl, 1), pxh = __shfl_up_sync(kFull, xh, 1);
-  if (lane == 0) { pxl = -2; pxh = -2; }
-  int nnew = (xl == pxl) ? 0 : ((xl == pxh) ? 1 : 2);
-  if (lane >= SX) nnew = 0;
-  int incl = nnew;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int v = __shfl_up_sync(kFull, incl, o);
-    if (lane >= o) incl += v;
-  }
-  const int base = incl - nnew;
-  const unsigned m1 = __ballot_sync(kFull, nnew == 1), m2 = __ballot_sync(kFull, nnew == 2);
-  const unsigned mv = __ballot_sync(kFull, t.valid && lane < SX);
-  if (lane < SX) {
-    xt.w[lane] = make_float2(t.wl, t.wh);
-    if (nnew == 2) {
-      xt.colofs[base] = xl * C;
-      xt.colofs[base + 1] = xh * C;
-    } else if (nnew == 1) {
-      xt.colofs[base] = xh * C;
-    }
-  }
-  if (lane == 31) {
-    xt.ncol = incl;
-    xt.m_slide = m1;
-    xt.m_reload = m2;
-    xt.m_valid = mv;
-  }
-}
-
-// ---- L2 prefetch of a RoI footprint ----------------------------------------------------
-// The rows of a RoI's footprint are contiguous NHWC segments (columns x channels).
-// Lane r asks the L2 to fetch row r of the footprint; no registers or shared
-// memory are tied up and nothing waits on it.
-template <typename T>
-__device__ __forceinline__ void prefetch_footprint(const LevelTable<T>& lv, const float* __restrict__ rois,
-                                                   const int32_t* __restrict__ levels, long long k, int nimg, int PH,
-                                                   int PW, int SR, bool aligned, int C, int lane) {
-  const int l = levels ? __ldg(levels + k) : 0;
-  const int H = lv.height[l], W = lv.width[l];
-  const RoiGeom<float> g = roi_geometry<float>(rois + k * 5, lv.scale[l], PH, PW, SR, aligned);
-  if (g.batch < 0 || g.batch >= nimg) return;
-  const float y0 = g.start_h, y1 = g.start_h + g.bin_h * (float)PH;
-  const float x0 = g.start_w, x1 = g.start_w + g.bin_w * (float)PW;
-  if (!(y1 >= -1.f && y0 <= (float)H && x1 >= -1.f && x0 <= (float)W)) return;  // also drops NaNs
-  const int ya = max((int)floorf(fmaxf(y0, 0.f)), 0), yb = min((int)floorf(fminf(y1, (float)H)) + 1, H - 1);
-  const int xa = max((int)floorf(fmaxf(x0, 0.f)), 0), xb = min((int)floorf(fminf(x1, (float)W)) + 1, W - 1);
-  if (xb < xa) return;
-  const unsigned bytes = (unsigned)((xb - xa + 1) * C * (int)sizeof(T));  // multiple of 16: C % 128 == 0
-  const T* img = lv.ptr[l] + (long long)g.batch * lv.sn[l];
-  for (int y = ya + lane; y <= yb; y += 32) {
-    const T* p = img + ((long long)y * W + xa) * C;
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
-  }
-}
-
-// ---- forward ---------------------------------------------------------------------------
-// Feature rows of ONE pooled row: 2*SR taps (lo/hi of each y sample), duplicates
-// merged into the first occurrence.  Every lane computes the same values, so no
-// shuffles or shared memory are involved.  off < 0 marks an unused slot.
-template <int SR>
-struct RowTaps {
-  int off[2 * SR];    // row * W * C (element offset inside the image), or -1
-  float w[2 * SR];    // merged weight, 1/count folded in
-};
-
-template <int SR>
-__device__ __forceinline__ RowTaps<SR> row_taps(const RoiGeom<float>& g, int H, int row_stride, int ph) {
-  RowTaps<SR> rt;
-  int row[2 * SR];
-#pragma unroll
-  for (int iy = 0; iy < SR; ++iy) {
-    const float y = sample_coord<float>(g.start_h, g.bin_h, ph, iy, SR);
-    const AxisTap<float> t = axis_tap<float>(y, H);
-    row[2 * iy] = t.valid ? t.lo : -1;
-    row[2 * iy + 1] = t.valid ? t.hi : -1;
-    rt.w[2 * iy] = t.wl * (1.0f / (float)(SR * SR));
-    rt.w[2 * iy + 1] = t.wh * (1.0f / (float)(SR * SR));
-  }
-#pragma unroll
-  for (int i = 1; i < 2 * SR; ++i) {
-    bool merged = false;
-#pragma unroll
-    for (int j = 0; j < i; ++j) {
-      if (!merged && row[i] >= 0 && row[i] == row[j]) {
-        rt.w[j] += rt.w[i];
-        merged = true;
-      }
-    }
-    if (merged) row[i] = -1;
-  }
-#pragma unroll
-  for (int i = 0; i < 2 * SR; ++i) rt.off[i] = row[i] >= 0 ? row[i] * row_stride : -1;
-  return rt;
-}
-
-template <typename T, int SR>
-__device__ __forceinline__ void issue_column(typename V4<T>::raw (&buf)[2 * SR], const RowTaps<SR>& rt,
-                                             const T* __restrict__ base, int co) {
-#pragma unroll
-  for (int r = 0; r < 2 * SR; ++r)
-    if (rt.off[r] >= 0) buf[r] = V4<T>::ldraw(base + (rt.off[r] + co));
-}
-
-template <typename T, int SR>
-__device__ __forceinline__ float4 vertical(const typename V4<T>::raw (&buf)[2 * SR], const RowTaps<SR>& rt) {
-  float4 v = f4zero();
-#pragma unroll
-  for (int r = 0; r < 2 * SR; ++r)
-    if (rt.off[r] >= 0) fma4(v, rt.w[r], V4<T>::cvt(buf[r]));
-  return v;
-}
-
-template <typename T, int SR>
-__global__ void __launch_bounds__(kFwdWarps * 32, 4) roi_align_fwd_sm100_kernel(
-    LevelTable<T> lv, const float* __restrict__ rois, const int32_t* __restrict__ levels, T* __restrict__ out,
-    int ntasks, int nimg, int C, int PH, int PW, bool aligned, int CT, int pf_dist) {
-  __shared__ XTable xt;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int task = blockIdx.x;
-  const int ct = task % CT;
-  const long long k = task / CT;
-  const int l = levels ? __ldg(levels + k) : 0;
-  const int H = lv.height[l], W = lv.width[l];
-  const RoiGeom<float> g = roi_geometry<float>(rois + k * 5, lv.scale[l], PH, PW, SR, aligned);
-  if (warp == 0) {
-    build_xtable<SR>(g, W, C, PW, lane, xt);
-  } else if (warp == 1 && ct == 0 && pf_dist > 0) {
-    const long long kp = k + pf_dist;
-    if (kp * CT < ntasks) prefetch_footprint<T>(lv, rois, levels, kp, nimg, PH, PW, SR, aligned, C, lane);
-  }
-  __syncthreads();
-  const int ncol = xt.ncol;
-  const unsigned m_slide = xt.m_slide, m_reload = xt.m_reload, m_valid = xt.m_valid;
-  const int ch = ct * 128 + lane * 4;
-  const T* base = lv.ptr[l] + (long long)g.batch * lv.sn[l] + ch;
-  T* obase = out + k * PH * PW * (long long)C + ch;
-
-  for (int ph = warp; ph < PH; ph += kFwdWarps) {
-    const RowTaps<SR> rt = row_taps<SR>(g, H, W * C, ph);
-    T* o = obase + (long long)ph * PW * C;
-
-    typename V4<T>::raw A[2 * SR], B[2 * SR];
-    int e = 0;
-    bool useA = true;
-    if (ncol > 0) issue_column<T, SR>(A, rt, base, xt.colofs[0]);
-    // vertical sum of column event e; the loads of event e+1 go out first
-    auto consume = [&]() -> float4 {
-      const int en = e + 1;
-      const bool more = en < ncol;
-      const int co_n = more ? xt.colofs[en] : 0;
-      float4 v;
-      if (useA) {
-        if (more) issue_column<T, SR>(B, rt, base, co_n);
-        v = vertical<T, SR>(A, rt);
-      } else {
-        if (more) issue_column<T, SR>(A, rt, base, co_n);
-        v = vertical<T, SR>(B, rt);
-      }
-      useA = !useA;
-      e = en;
-      return v;
-    };
-
-    float4 lo = f4zero(), hi = f4zero();
-    for (int pw = 0; pw < PW; ++pw) {
-      float4 a = f4zero();
-#pragma unroll
-      for (int s = 0; s < SR; ++s) {
-        const int j = pw * SR + s;
-        const unsigned bit = 1u << j;
-        if (m_reload & bit) {
-          lo = consume();
-          hi = consume();
-        } else if (m_slide & bit) {
-          lo = hi;
-          hi = consume();
-        }
-        if (m_valid & bit) {
-          const float2 w = xt.w[j];
-          fma4(a, w.x, lo);
-          fma4(a, w.y, hi);
-        }
-      }
-      V4<T>::st(o + (long long)pw * C, a);
-    }
-  }
 }
 
 // ---- backward --------------------------------------------------------------------------
@@ -489,70 +247,10 @@ __global__ void __launch_bounds__(kBwdWarps * 32) roi_align_bwd_sm100_kernel(
 }
 
 template <typename T>
-LevelTable<T> make_table(const LevelArgs& a) {
-  LevelTable<T> t;
-  t.num_levels = a.num_levels;
-  for (int l = 0; l < B200DET_MAX_LEVELS; ++l) {
-    const int s = l < a.num_levels ? l : 0;
-    t.ptr[l] = (T*)a.ptr[s];
-    t.height[l] = (int)a.height[s];
-    t.width[l] = (int)a.width[s];
-    t.scale[l] = (float)a.scale[s];
-    const long long C = a.channels, H = a.height[s], W = a.width[s];
-    t.sn[l] = H * W * C; t.sc[l] = 1; t.sh[l] = W * C; t.sw[l] = C;
-  }
-  return t;
-}
-
-bool eligible(const LevelArgs& lv, int dtype, int PH, int PW, int sr) {
-  if (dtype == B200DET_F64) return false;
-  if (lv.layout != B200DET_NHWC) return false;
-  if (lv.channels % 128 != 0) return false;
-  if (sr != 1 && sr != 2) return false;
-  if (PW * sr > kMaxSX || PH < 1 || PW < 1) return false;
-  const size_t es = dtype_size(dtype);
-  for (int l = 0; l < lv.num_levels; ++l) {
-    if (lv.height[l] < 1 || lv.width[l] < 1) return false;
-    if (lv.height[l] * lv.width[l] * lv.channels >= (1LL << 31)) return false;  // 32-bit in-image offsets
-    if (((uintptr_t)lv.ptr[l]) % (4 * es) != 0) return false;                   // vector alignment
-  }
-  return true;
-}
-
-// How many RoIs ahead the forward prefetches into L2.  Measured on B200 (kbench, r01): the
-// prefetch LOSES (cfg3 fp32 fwd 0.70 ms off vs 0.78 ms at the old default, cfg1 0.09 vs 0.24 ms),
-// so it is off unless B200DET_PF_DIST=<RoIs ahead> asks for it.
-int prefetch_distance(int CT) {
-  static int env = -2;
-  if (env == -2) {
-    const char* s = getenv("B200DET_PF_DIST");
-    env = s ? atoi(s) : -1;
-  }
-  if (env >= 0) return env;
-  (void)CT;
-  return 0;
-}
-
-template <typename T>
-int launch_fwd(const LevelArgs& lv, const void* rois, const int32_t* levels, void* out, long long tasks, int C,
-               int PH, int PW, int sr, bool aligned, int CT, cudaStream_t st) {
-  const LevelTable<T> tab = make_table<T>(lv);
-  const int pf = prefetch_distance(CT);
-  if (sr == 1)
-    roi_align_fwd_sm100_kernel<T, 1><<<(unsigned)tasks, kFwdWarps * 32, 0, st>>>(
-        tab, (const float*)rois, levels, (T*)out, (int)tasks, (int)lv.batch, C, PH, PW, aligned, CT, pf);
-  else
-    roi_align_fwd_sm100_kernel<T, 2><<<(unsigned)tasks, kFwdWarps * 32, 0, st>>>(
-        tab, (const float*)rois, levels, (T*)out, (int)tasks, (int)lv.batch, C, PH, PW, aligned, CT, pf);
-  B200DET_CUDA_OK(cudaGetLastError());
-  return 0;
-}
-
-template <typename T>
 int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool vec, const void* rois,
                const int32_t* levels, long long tasks, int C, int PH, int PW, int sr, bool aligned, int CT, int RP,
                cudaStream_t st) {
-  const LevelTable<T> tab = make_table<T>(lv);
+  const LevelTable<T> tab = make_nhwc_table<T>(lv);
   const unsigned blocks = (unsigned)((tasks + kBwdWarps - 1) / kBwdWarps);
   if (sr == 1)
     roi_align_bwd_sm100_kernel<T, 1><<<blocks, kBwdWarps * 32, 0, st>>>(
@@ -568,33 +266,11 @@ int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool ve
 
 }  // namespace
 
-int roi_align_fwd_fast(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels, void* out,
-                       int out_layout, long long K, int PH, int PW, int sr, bool aligned, cudaStream_t st,
-                       int* taken) {
-  *taken = 0;
-  if (!eligible(lv, dtype, PH, PW, sr) || out_layout != B200DET_NHWC) return 0;
-  if (((uintptr_t)out) % (4 * dtype_size(dtype)) != 0) return 0;
-  const int C = (int)lv.channels, CT = C / 128;
-  const long long tasks = K * CT;
-  if (tasks == 0) { *taken = 1; return 0; }
-  if (tasks > 0x7fffffffLL) return 0;
-  int rc = 0;
-  switch (dtype) {
-    case B200DET_F32: rc = launch_fwd<float>(lv, rois, levels, out, tasks, C, PH, PW, sr, aligned, CT, st); break;
-    case B200DET_F16: rc = launch_fwd<__half>(lv, rois, levels, out, tasks, C, PH, PW, sr, aligned, CT, st); break;
-    case B200DET_BF16: rc = launch_fwd<__nv_bfloat16>(lv, rois, levels, out, tasks, C, PH, PW, sr, aligned, CT, st); break;
-    default: return 0;
-  }
-  if (rc) return rc;
-  *taken = 1;
-  return 0;
-}
-
 int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs, const void* rois,
                        const int32_t* levels, long long K, int PH, int PW, int sr, bool aligned,
                        cudaStream_t st, int* taken) {
   *taken = 0;
-  if (!eligible(lv, dtype, PH, PW, sr)) return 0;
+  if (!sm100_eligible(lv, dtype, PH, PW, sr)) return 0;
   const size_t es = dtype_size(dtype);
   // vector loads of the gradient need unit channel stride and 4-element alignment of every row start
   const bool vec = gs[1] == 1 && gs[0] % 4 == 0 && gs[2] % 4 == 0 && gs[3] % 4 == 0 &&
