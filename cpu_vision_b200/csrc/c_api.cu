@@ -88,18 +88,21 @@ static int forward_impl(const LevelArgs& lv, int dtype, const void* rois, const 
 static int backward_impl(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
                          const void* rois, const int32_t* levels, int64_t K, int64_t PH, int64_t PW,
                          int sr, int aligned, int zero_init, cudaStream_t st) {
+  const bool work = K * lv.channels * PH * PW != 0;
+  if (work) {
+    if (!rois || !grad || !gs) return fail(B200DET_EINVAL, "roi_align backward: null pointer");
+    int taken = 0;  // the sm_100a path fuses the zero fill with the scatter
+    int rc = roi_align_bwd_fast(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
+                                zero_init != 0, st, &taken);
+    if (rc != 0 || taken) return rc;
+  }
   if (zero_init) {
     for (int l = 0; l < lv.num_levels; ++l) {
       const size_t bytes = (size_t)lv.batch * lv.channels * lv.height[l] * lv.width[l] * dtype_size(dtype);
       if (bytes) B200DET_CUDA_OK(cudaMemsetAsync(lv.ptr[l], 0, bytes, st));
     }
   }
-  if (K * lv.channels * PH * PW == 0) return 0;
-  if (!rois || !grad || !gs) return fail(B200DET_EINVAL, "roi_align backward: null pointer");
-  int taken = 0;
-  int rc = roi_align_bwd_fast(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr,
-                              aligned != 0, st, &taken);
-  if (rc != 0 || taken) return rc;
+  if (!work) return 0;
   return roi_align_bwd_generic(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr,
                                aligned != 0, st);
 }

@@ -31,14 +31,16 @@ int roi_align_bwd_generic(const LevelArgs& lv, int dtype, const void* grad, cons
 int fpn_level_map(const void* rois, int dtype, long long K, int k_min, int k_max, int s0, int lvl0,
                   double eps, int32_t* levels, cudaStream_t st);
 
-// roi_align_sm100.cu: returns 1 when it took the call, 0 when the generic path
+// roi_align_fwd_sm100.cu / roi_align_bwd_sm100.cu: returns 1 when it took the call, 0 when the generic path
 // must run, <0 / >0 on error like the public API.
 int roi_align_fwd_fast(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
                        void* out, int out_layout, long long K, int PH, int PW, int sr,
                        bool aligned, cudaStream_t st, int* taken);
+// The backward zero-fills the gradients itself when zero_init is set (fused with the scatter).
 int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
                        const void* rois, const int32_t* levels, long long K, int PH, int PW,
-                       int sr, bool aligned, cudaStream_t st, int* taken);
+                       int sr, bool aligned, bool zero_init, cudaStream_t st, int* taken);
+void roi_align_bwd_release();
 
 // nms_sm100.cu
 size_t nms_workspace_bytes(long long N);

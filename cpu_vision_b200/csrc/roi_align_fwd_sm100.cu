@@ -45,69 +45,12 @@ int fwd_warps() {
   }
   return nw;
 }
-constexpr int kMaxEvents = 2 * kMaxSX;
-
 struct __align__(16) FwdTables {
-  float4 samp[kMaxSX];                  // (hx, lx, valid as 0/1 bits, -): weights of the lo / hi column
-  int colofs[kMaxEvents + 2];           // element offset (x * C) of column event e; 2 entries of padding
-  unsigned char ev_end[kMaxEvents + 4]; // [e + 1]: samples complete once event e arrived; [0]: before any
-  int ncol;
+  XTab x;
   int y_nr[kMaxPH];                     // distinct feature rows of pooled row ph
   int y_off[kMaxPH][4];                 // row * W * C
   float y_w[kMaxPH][4];                 // merged weight / count
 };
-
-// ---- x axis (warp 0; lane j owns x sample j) ------------------------------------------
-// The sweep keeps a window of two feature columns (lo, hi = min(lo + 1, W - 1),
-// clamped like roi_align_kernel.cu:34-46).  A sample finds its taps by leaving
-// the window as it is, shifting it by one column (one event) or refilling it
-// (two events).  Empty samples (roi_align_kernel.cu:23-26) fetch nothing.
-template <int SR>
-__device__ __forceinline__ void build_x(const RoiGeom<float>& g, int W, int C, int PW, int lane, FwdTables& tb) {
-  const int SX = PW * SR;
-  const bool active = lane < SX;
-  const int j = active ? lane : SX - 1;
-  const float x = sample_coord<float>(g.start_w, g.bin_w, j / SR, j % SR, SR);
-  const AxisTap<float> t = axis_tap<float>(x, W);
-  const bool valid = t.valid && active;
-  const int xl = t.lo, xh = min(t.lo + 1, W - 1);
-  // window left by the last valid sample before this one
-  const unsigned vmask = __ballot_sync(kFull, valid);
-  const unsigned before = vmask & ((1u << lane) - 1u);
-  const int p = before ? 31 - __clz(before) : 0;
-  int pxl = __shfl_sync(kFull, xl, p), pxh = __shfl_sync(kFull, xh, p);
-  if (!before) { pxl = -2; pxh = -2; }
-  const int nnew = !valid ? 0 : (xl == pxl ? 0 : (xl == pxh ? 1 : 2));
-  int incl = nnew;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int v = __shfl_up_sync(kFull, incl, o);
-    if (lane >= o) incl += v;
-  }
-  const int base = incl - nnew;
-  const int ncol = __shfl_sync(kFull, incl, 31);
-  if (active) {
-    tb.samp[lane] = make_float4(t.wl, t.wh, __int_as_float(valid ? 1 : 0), 0.f);
-    if (nnew == 2) {
-      tb.colofs[base] = xl * C;
-      tb.colofs[base + 1] = xh * C;
-    } else if (nnew == 1) {
-      tb.colofs[base] = xh * C;
-    }
-  }
-  // sample j is complete after event last = incl - 1 (-1: needs no event at all)
-  const int last = incl - 1;
-  int nxt = __shfl_down_sync(kFull, last, 1);
-  if (lane == SX - 1) nxt = ncol;
-  if (active) {
-    for (int e = last; e < nxt; ++e) tb.ev_end[e + 1] = (unsigned char)(lane + 1);
-    if (lane == 0)
-      for (int e = -1; e < last; ++e) tb.ev_end[e + 1] = 0;
-  }
-  if (lane == 0) tb.ncol = ncol;
-  __syncwarp();
-  if (lane < 2 && ncol > 0) tb.colofs[ncol + lane] = tb.colofs[ncol - 1];
-}
 
 // ---- y axis (warp 1; lane = pooled row) --------------------------------------------------
 // 2*SR taps (lo / hi of each y sample) in ascending order; equal neighbours are
@@ -183,7 +126,7 @@ __device__ __forceinline__ void sweep_row(const FwdTables& tb, const T* __restri
   // samples j .. end-1 read the window (lo, hi); a bin is stored when its last sample is done
   auto samples = [&](int end, const f32x2 (&lo)[H2], const f32x2 (&hi)[H2]) {
     for (; j < end; ++j) {
-      const float4 s = tb.samp[j];
+      const float4 s = tb.x.samp[j];
       if (__float_as_int(s.z)) {
         const f32x2 hx = pack2(s.x, s.x), lx = pack2(s.y, s.y);
 #pragma unroll
@@ -198,24 +141,24 @@ __device__ __forceinline__ void sweep_row(const FwdTables& tb, const T* __restri
     }
   };
 
-  const int ncol = tb.ncol;
-  samples(tb.ev_end[0], X, Y);
+  const int ncol = tb.x.ncol;
+  samples(tb.x.ev_end[0], X, Y);
   if (ncol > 0) {
     // colofs[] is padded with two copies of its last entry, so the refills past the
     // end re-read a column that is already in L1 instead of branching
 #pragma unroll
-    for (int r = 0; r < NR; ++r) A[r] = LV::ld(rp[r] + tb.colofs[0]);
+    for (int r = 0; r < NR; ++r) A[r] = LV::ld(rp[r] + tb.x.colofs[0]);
 #pragma unroll
-    for (int r = 0; r < NR; ++r) B[r] = LV::ld(rp[r] + tb.colofs[1]);
+    for (int r = 0; r < NR; ++r) B[r] = LV::ld(rp[r] + tb.x.colofs[1]);
     int e = 0;
     while (true) {
       // event e sits in A and becomes X: window = (lo Y, hi X)
-      vertical_refill(A, X, tb.colofs[e + 2]);
-      samples(tb.ev_end[e + 1], Y, X);
+      vertical_refill(A, X, tb.x.colofs[e + 2]);
+      samples(tb.x.ev_end[e + 1], Y, X);
       if (++e >= ncol) break;
       // event e sits in B and becomes Y: window = (lo X, hi Y)
-      vertical_refill(B, Y, tb.colofs[e + 2]);
-      samples(tb.ev_end[e + 1], X, Y);
+      vertical_refill(B, Y, tb.x.colofs[e + 2]);
+      samples(tb.x.ev_end[e + 1], X, Y);
       if (++e >= ncol) break;
     }
   }
@@ -233,7 +176,7 @@ __global__ void __launch_bounds__(256, 2) roi_align_fwd_sm100_kernel(
   const int l = levels ? __ldg(levels + k) : 0;
   const int H = lv.height[l], W = lv.width[l];
   const RoiGeom<float> g = roi_geometry<float>(rois + k * 5, lv.scale[l], PH, PW, SR, aligned);
-  if (warp == 0) build_x<SR>(g, W, C, PW, lane, tb);
+  if (warp == 0) build_x<SR>(g, W, C, PW, lane, tb.x);
   else if (warp == 1) build_y<SR>(g, H, W * C, PH, lane, tb);
   __syncthreads();
   const int ch = ct * (32 * CH) + lane_channel<T, CH>(lane);

@@ -34,6 +34,14 @@ __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
   return d;
 }
 
+// one vector reduction per 16 bytes: red.global.add.v4.f32 (sm_90+)
+__device__ __forceinline__ void red_v4_f32(float* p, f32x2 a, f32x2 b) {
+  float x, y, z, w;
+  unpack2(a, x, y);
+  unpack2(b, z, w);
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+
 // ---- the channels one lane owns at one pixel ------------------------------------
 // CH channels per lane (4 or 8), held as CH/2 packed pairs once converted.
 // Raw<T, CH> is what one pixel's load leaves in registers.
@@ -47,6 +55,7 @@ template <> struct LaneVec<float, 4> {
   static __device__ __forceinline__ void st(float* p, const f32x2 (&v)[2]) {
     __stcs(reinterpret_cast<ulonglong2*>(p), make_ulonglong2(v[0], v[1]));
   }
+  static __device__ __forceinline__ void red(float* p, const f32x2 (&v)[2]) { red_v4_f32(p, v[0], v[1]); }
 };
 template <> struct LaneVec<float, 8> {
   // channels [4*lane, +4) and [128 + 4*lane, +4) of a 256-channel tile: two
@@ -65,6 +74,10 @@ template <> struct LaneVec<float, 8> {
     __stcs(reinterpret_cast<ulonglong2*>(p), make_ulonglong2(v[0], v[1]));
     __stcs(reinterpret_cast<ulonglong2*>(p + 128), make_ulonglong2(v[2], v[3]));
   }
+  static __device__ __forceinline__ void red(float* p, const f32x2 (&v)[4]) {
+    red_v4_f32(p, v[0], v[1]);
+    red_v4_f32(p + 128, v[2], v[3]);
+  }
 };
 
 // 16-bit element <-> fp32 pair conversions
@@ -80,6 +93,12 @@ template <> struct Cvt16<__nv_bfloat16> {
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<const unsigned*>(&h);
   }
+  static __device__ __forceinline__ void red2(__nv_bfloat16* p, unsigned a, unsigned b) {
+    asm volatile("red.global.add.noftz.v2.bf16x2 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+  }
+  static __device__ __forceinline__ void red4(__nv_bfloat16* p, unsigned a, unsigned b, unsigned c, unsigned d) {
+    asm volatile("red.global.add.noftz.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+  }
 };
 template <> struct Cvt16<__half> {
   static __device__ __forceinline__ f32x2 widen(unsigned u) {
@@ -92,6 +111,12 @@ template <> struct Cvt16<__half> {
     const __half2 h = __floats2half2_rn(a, b);
     return *reinterpret_cast<const unsigned*>(&h);
   }
+  static __device__ __forceinline__ void red2(__half* p, unsigned a, unsigned b) {
+    asm volatile("red.global.add.noftz.v2.f16x2 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+  }
+  static __device__ __forceinline__ void red4(__half* p, unsigned a, unsigned b, unsigned c, unsigned d) {
+    asm volatile("red.global.add.noftz.v4.f16x2 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+  }
 };
 
 template <typename T> struct LaneVec16x4 {
@@ -103,6 +128,9 @@ template <typename T> struct LaneVec16x4 {
   }
   static __device__ __forceinline__ void st(T* p, const f32x2 (&v)[2]) {
     __stcs(reinterpret_cast<uint2*>(p), make_uint2(Cvt16<T>::narrow(v[0]), Cvt16<T>::narrow(v[1])));
+  }
+  static __device__ __forceinline__ void red(T* p, const f32x2 (&v)[2]) {
+    Cvt16<T>::red2(p, Cvt16<T>::narrow(v[0]), Cvt16<T>::narrow(v[1]));
   }
 };
 template <typename T> struct LaneVec16x8 {
@@ -118,6 +146,9 @@ template <typename T> struct LaneVec16x8 {
     __stcs(reinterpret_cast<uint4*>(p), make_uint4(Cvt16<T>::narrow(v[0]), Cvt16<T>::narrow(v[1]),
                                                     Cvt16<T>::narrow(v[2]), Cvt16<T>::narrow(v[3])));
   }
+  static __device__ __forceinline__ void red(T* p, const f32x2 (&v)[4]) {
+    Cvt16<T>::red4(p, Cvt16<T>::narrow(v[0]), Cvt16<T>::narrow(v[1]), Cvt16<T>::narrow(v[2]), Cvt16<T>::narrow(v[3]));
+  }
 };
 template <> struct LaneVec<__half, 4> : LaneVec16x4<__half> {};
 template <> struct LaneVec<__half, 8> : LaneVec16x8<__half> {};
@@ -129,6 +160,68 @@ template <> struct LaneVec<__nv_bfloat16, 8> : LaneVec16x8<__nv_bfloat16> {};
 template <typename T, int CH>
 __device__ __forceinline__ int lane_channel(int lane) {
   return (sizeof(T) == 4) ? lane * 4 : lane * CH;
+}
+
+// ---- x axis tables -----------------------------------------------------------------------
+constexpr int kMaxEvents = 2 * kMaxSX;
+
+struct __align__(16) XTab {
+  float4 samp[kMaxSX];                  // (hx, lx, valid as 0/1 bits, -): weights of the lo / hi column
+  int colofs[kMaxEvents + 2];           // element offset (x * C) of column event e; 2 entries of padding
+  unsigned char ev_end[kMaxEvents + 4]; // [e + 1]: samples complete once event e arrived; [0]: before any
+  int ncol;
+};
+
+// ---- x axis (one warp; lane j owns x sample j) ------------------------------------------
+// The sweep keeps a window of two feature columns (lo, hi = min(lo + 1, W - 1),
+// clamped like roi_align_kernel.cu:34-46).  A sample finds its taps by leaving
+// the window as it is, shifting it by one column (one event) or refilling it
+// (two events).  Empty samples (roi_align_kernel.cu:23-26) fetch nothing.
+template <int SR>
+__device__ __forceinline__ void build_x(const RoiGeom<float>& g, int W, int C, int PW, int lane, XTab& tb) {
+  const int SX = PW * SR;
+  const bool active = lane < SX;
+  const int j = active ? lane : SX - 1;
+  const float x = sample_coord<float>(g.start_w, g.bin_w, j / SR, j % SR, SR);
+  const AxisTap<float> t = axis_tap<float>(x, W);
+  const bool valid = t.valid && active;
+  const int xl = t.lo, xh = min(t.lo + 1, W - 1);
+  // window left by the last valid sample before this one
+  const unsigned vmask = __ballot_sync(kFull, valid);
+  const unsigned before = vmask & ((1u << lane) - 1u);
+  const int p = before ? 31 - __clz(before) : 0;
+  int pxl = __shfl_sync(kFull, xl, p), pxh = __shfl_sync(kFull, xh, p);
+  if (!before) { pxl = -2; pxh = -2; }
+  const int nnew = !valid ? 0 : (xl == pxl ? 0 : (xl == pxh ? 1 : 2));
+  int incl = nnew;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(kFull, incl, o);
+    if (lane >= o) incl += v;
+  }
+  const int base = incl - nnew;
+  const int ncol = __shfl_sync(kFull, incl, 31);
+  if (active) {
+    tb.samp[lane] = make_float4(t.wl, t.wh, __int_as_float(valid ? 1 : 0), 0.f);
+    if (nnew == 2) {
+      tb.colofs[base] = xl * C;
+      tb.colofs[base + 1] = xh * C;
+    } else if (nnew == 1) {
+      tb.colofs[base] = xh * C;
+    }
+  }
+  // sample j is complete after event last = incl - 1 (-1: needs no event at all)
+  const int last = incl - 1;
+  int nxt = __shfl_down_sync(kFull, last, 1);
+  if (lane == SX - 1) nxt = ncol;
+  if (active) {
+    for (int e = last; e < nxt; ++e) tb.ev_end[e + 1] = (unsigned char)(lane + 1);
+    if (lane == 0)
+      for (int e = -1; e < last; ++e) tb.ev_end[e + 1] = 0;
+  }
+  if (lane == 0) tb.ncol = ncol;
+  __syncwarp();
+  if (lane < 2 && ncol > 0) tb.colofs[ncol + lane] = tb.colofs[ncol - 1];
 }
 
 // ---- host helpers --------------------------------------------------------------------
