@@ -5,7 +5,9 @@
  * (cpu_vision_b200/csrc/torch_shim.cpp).  Every entry point takes plain
  * pointers, sizes and a cudaStream_t passed as void*; no torch types appear.
  * Nothing here allocates device memory unless the name ends in `_host`
- * (those own a private staging arena, see below).
+ * (those own a private staging arena, see below), with one exception: the
+ * first *_backward call on a device creates a 2 MB ring of task plans for the
+ * persistent backward kernel; b200det_host_release() frees it.
  *
  * Each function names the reference interface it replaces; paths are relative
  * to the reference tree (kaisun24/CPU-Vision, a torchvision 0.20 fork).

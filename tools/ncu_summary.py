@@ -1,0 +1,107 @@
+#!/usr/bin/env python
+"""Text summary of an .ncu-rep (run here, no GPU needed): key raw metrics per kernel, the SASS
+opcode mix and the most-stalled instructions.  Output is what gets committed under profiles/.
+
+    python tools/ncu_summary.py gpurun_out/x.ncu-rep > profiles/x.ncu.txt
+"""
+import collections
+import csv
+import subprocess
+import sys
+
+KEYS = [
+    "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+    "sm__warps_active.avg.pct_of_peak_sustained_active",
+    "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+    "lts__t_sector_hit_rate.pct", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+    "lts__t_sectors_srcunit_tex_op_read.sum", "lts__t_sectors_srcunit_tex_op_write.sum",
+    "lts__t_sectors_srcunit_tex_op_red.sum", "lts__t_sectors_srcunit_tex_op_red_lookup_hit.sum",
+    "lts__t_sectors_srcunit_tex_op_red_lookup_miss.sum", "lts__d_atomic_input_cycles_active.avg.pct_of_peak_sustained_elapsed",
+    "l1tex__t_sector_hit_rate.pct", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+    "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed",
+    "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+]
+
+
+def ncu(rep, page):
+    return subprocess.run(["ncu", "-i", rep, "--page", page, "--csv"], capture_output=True, text=True).stdout
+
+
+def raw(rep):
+    rows = list(csv.reader(ncu(rep, "raw").splitlines()))
+    hdr, units = rows[0], rows[1]
+    for r in rows[2:]:
+        print("=" * 100)
+        print("kernel:", r[hdr.index("Kernel Name")])
+        for k in KEYS:
+            if k in hdr:
+                i = hdr.index(k)
+                print(f"  {k:82s} {r[i]} {units[i]}")
+
+
+def source(rep, top=16):
+    out = ncu(rep, "source")
+    blocks, cur = [], []
+    for line in out.splitlines():
+        if line.startswith('"Kernel Name"'):
+            if cur:
+                blocks.append(cur)
+            cur = [line]
+        elif cur:
+            cur.append(line)
+    if cur:
+        blocks.append(cur)
+    seen = set()
+    for b in blocks:
+        name = next(csv.reader([b[0]]))[1]
+        if name in seen:
+            continue
+        seen.add(name)
+        rows = list(csv.reader(b[1:]))
+        hdr = rows[0]
+        iS, iE, iN = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("# Samples")
+        stall_cols = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
+        ops, samp, stalls, data = collections.Counter(), collections.Counter(), collections.Counter(), []
+        tot = tots = 0
+        for r in rows[1:]:
+            if len(r) < len(hdr):
+                continue
+            try:
+                e, s = int(r[iE]), int(r[iN])
+            except ValueError:
+                continue
+            toks = r[iS].split()
+            op = toks[1] if toks[0].startswith("@") else toks[0]
+            parts = op.split(".")
+            op = parts[0] + ("." + ".".join(parts[1:3]) if parts[0] in ("LDG", "STG", "RED", "LDS", "STS") else "")
+            ops[op] += e
+            samp[op] += s
+            tot += e
+            tots += s
+            for i in stall_cols:
+                try:
+                    stalls[hdr[i]] += int(r[i])
+                except ValueError:
+                    pass
+            data.append((s, e, r[iS]))
+        print("=" * 100)
+        print("kernel:", name)
+        print(f"  warp instructions executed {tot}, stall samples {tots}")
+        print("  opcode mix (share of instructions | share of stall samples):")
+        for op, c in ops.most_common(14):
+            print(f"    {op:16s} {100 * c / max(tot, 1):5.1f}% | {100 * samp[op] / max(tots, 1):5.1f}%")
+        print("  stall reasons:", ", ".join(f"{k[6:]} {100 * v / max(tots, 1):.0f}%" for k, v in stalls.most_common(6)))
+        print("  most-sampled instructions (samples, executed, SASS):")
+        for s, e, src in sorted(data, reverse=True)[:top]:
+            print(f"    {s:7d} {e:10d}  {src}")
+
+
+if __name__ == "__main__":
+    rep = sys.argv[1]
+    print(f"# ncu summary of {rep} (ncu --set full --clock-control none --import-source on; cold-cache, serialised)")
+    raw(rep)
+    source(rep)
