@@ -121,7 +121,7 @@ def roi_align_forward(x, rois, pooled_h, pooled_w, spatial_scale=1.0, sampling_r
 
 
 def roi_align_backward(grad, rois, spatial_scale, pooled_h, pooled_w, N, Cc, H, W, sampling_ratio, aligned,
-                       layout=NCHW, out=None, zero_init=True):
+                       layout=NCHW, out=None, zero_init=True, deterministic=False):
     assert grad.is_cuda and rois.is_cuda
     r = _arith(rois, grad.dtype)
     gi = out if out is not None else _empty_like_layout((N, Cc, H, W), grad, layout)
@@ -129,7 +129,7 @@ def roi_align_backward(grad, rois, spatial_scale, pooled_h, pooled_w, N, Cc, H, 
         _check(lib().b200det_roi_align_backward(grad.data_ptr(), _strides(grad), r.data_ptr(), gi.data_ptr(), layout,
                                                 _dt(grad), N, Cc, H, W, r.shape[0], pooled_h, pooled_w,
                                                 float(spatial_scale), int(sampling_ratio), int(bool(aligned)),
-                                                int(bool(zero_init)), _stream(grad)),
+                                                int(bool(zero_init)) | (2 if deterministic else 0), _stream(grad)),
                "b200det_roi_align_backward")
     return gi
 
@@ -176,7 +176,7 @@ def msroi_align_forward(feats: List[torch.Tensor], rois, scales, pooled_h, poole
 
 
 def msroi_align_backward(grad, rois, levels, scales, shapes, pooled_h, pooled_w, sampling_ratio, aligned=False,
-                         layout=NCHW, outs=None, zero_init=True):
+                         layout=NCHW, outs=None, zero_init=True, deterministic=False):
     """shapes: [(N,C,H,W)] per level -> list of gradients in `layout`."""
     r = _arith(rois, grad.dtype)
     if outs is None:
@@ -187,7 +187,7 @@ def msroi_align_backward(grad, rois, levels, scales, shapes, pooled_h, pooled_w,
         _check(lib().b200det_msroi_align_backward(grad.data_ptr(), _strides(grad), r.data_ptr(), levels.data_ptr(),
                                                   ptrs, hs, ws, sc, len(outs), layout, _dt(grad), N, Cc, r.shape[0],
                                                   pooled_h, pooled_w, int(sampling_ratio), int(bool(aligned)),
-                                                  int(bool(zero_init)), _stream(grad)),
+                                                  int(bool(zero_init)) | (2 if deterministic else 0), _stream(grad)),
                "b200det_msroi_align_backward")
     return outs
 

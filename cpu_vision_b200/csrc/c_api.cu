@@ -3,6 +3,7 @@
 // kernels are in roi_align_sm100.cu / roi_align_generic.cu / nms_sm100.cu.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -87,13 +88,27 @@ static int forward_impl(const LevelArgs& lv, int dtype, const void* rois, const 
 
 static int backward_impl(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
                          const void* rois, const int32_t* levels, int64_t K, int64_t PH, int64_t PW,
-                         int sr, int aligned, int zero_init, cudaStream_t st) {
+                         int sr, int aligned, int flags, cudaStream_t st) {
+  const bool zero_init = (flags & B200DET_BWD_ZERO_INIT) != 0;
+  const bool deterministic = (flags & B200DET_BWD_DETERMINISTIC) != 0;
   const bool work = K * lv.channels * PH * PW != 0;
   if (work) {
     if (!rois || !grad || !gs) return fail(B200DET_EINVAL, "roi_align backward: null pointer");
-    int taken = 0;  // the sm_100a path fuses the zero fill with the scatter
-    int rc = roi_align_bwd_fast(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
-                                zero_init != 0, st, &taken);
+    int taken = 0;
+    int rc = 0;
+    static const bool tile_env = getenv("B200DET_BWD_TILE") && atoi(getenv("B200DET_BWD_TILE")) != 0;
+    if (deterministic || tile_env) {  // tile accumulation: every byte written once, fixed order
+      rc = roi_align_bwd_tile(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
+                              zero_init, st, &taken);
+      if (rc != 0 || taken) return rc;
+      if (deterministic)
+        return fail(B200DET_ENOSUP,
+                    "roi_align backward: the deterministic kernel needs channels_last tensors, C %% 128 == 0, "
+                    "sampling_ratio 1 or 2 and a channel-contiguous gradient");
+    }
+    // fused zero fill + vector-red scatter
+    rc = roi_align_bwd_fast(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
+                            zero_init, st, &taken);
     if (rc != 0 || taken) return rc;
   }
   if (zero_init) {
@@ -134,7 +149,7 @@ int b200det_roi_align_backward(const void* grad, const int64_t* grad_strides, co
                                void* grad_input, int gi_layout, int dtype, int64_t N, int64_t C,
                                int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
                                double spatial_scale, int sampling_ratio, int aligned,
-                               int zero_init, void* stream) {
+                               int flags, void* stream) {
   int rc = check_common("roi_align_backward", dtype, gi_layout, gi_layout, N, C, K, PH, PW);
   if (rc) return rc;
   LevelArgs lv;
@@ -142,7 +157,7 @@ int b200det_roi_align_backward(const void* grad, const int64_t* grad_strides, co
   rc = fill_levels("roi_align_backward", lv, feats, &H, &W, &spatial_scale, 1, gi_layout, N, C);
   if (rc) return rc;
   return backward_impl(lv, dtype, grad, grad_strides, rois, nullptr, K, PH, PW, sampling_ratio,
-                       aligned, zero_init, (cudaStream_t)stream);
+                       aligned, flags, (cudaStream_t)stream);
 }
 
 int b200det_fpn_level_map(const void* rois, int dtype, int64_t K, int k_min, int k_max,
@@ -188,7 +203,7 @@ int b200det_msroi_align_backward(const void* grad, const int64_t* grad_strides, 
                                  const int64_t* heights, const int64_t* widths,
                                  const double* scales, int num_levels, int layout, int dtype,
                                  int64_t N, int64_t C, int64_t K, int64_t PH, int64_t PW,
-                                 int sampling_ratio, int aligned, int zero_init, void* stream) {
+                                 int sampling_ratio, int aligned, int flags, void* stream) {
   int rc = check_common("msroi_align_backward", dtype, layout, layout, N, C, K, PH, PW);
   if (rc) return rc;
   if (!grad_feats || !heights || !widths || !scales)
@@ -200,7 +215,7 @@ int b200det_msroi_align_backward(const void* grad, const int64_t* grad_strides, 
   if (num_levels > 1 && K > 0 && !levels)
     return fail(B200DET_EINVAL, "msroi_align_backward: levels required");
   return backward_impl(lv, dtype, grad, grad_strides, rois, num_levels > 1 ? levels : nullptr, K, PH,
-                       PW, sampling_ratio, aligned, zero_init, (cudaStream_t)stream);
+                       PW, sampling_ratio, aligned, flags, (cudaStream_t)stream);
 }
 
 size_t b200det_nms_workspace_bytes(int64_t N) { return nms_workspace_bytes(N); }

@@ -41,6 +41,11 @@ int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const i
                        const void* rois, const int32_t* levels, long long K, int PH, int PW,
                        int sr, bool aligned, bool zero_init, cudaStream_t st, int* taken);
 void roi_align_bwd_release();
+// roi_align_bwd_tile_sm100.cu: tile-accumulating backward (no atomics, deterministic); same contract
+int roi_align_bwd_tile(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
+                       const void* rois, const int32_t* levels, long long K, int PH, int PW,
+                       int sr, bool aligned, bool zero_init, cudaStream_t st, int* taken);
+void roi_align_bwd_tile_release();
 
 // nms_sm100.cu
 size_t nms_workspace_bytes(long long N);

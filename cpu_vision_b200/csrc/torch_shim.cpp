@@ -118,14 +118,23 @@ at::Tensor roi_align_backward_cuda(const at::Tensor& grad, const at::Tensor& roi
       {batch_size, channels, height, width},
       grad.options().memory_format(nhwc ? at::MemoryFormat::ChannelsLast : at::MemoryFormat::Contiguous));
   if (grad.numel() == 0) return grad_input.zero_();
-  at::globalContext().alertNotDeterministic("roi_align_backward_kernel");
   const at::Tensor rois_ = arith_rois(rois, grad.scalar_type());
   const int64_t gs[4] = {grad.stride(0), grad.stride(1), grad.stride(2), grad.stride(3)};
-  check_rc(b200det_roi_align_backward(grad.data_ptr(), gs, rois_.data_ptr(), grad_input.data_ptr(),
-                                      nhwc ? B200DET_NHWC : B200DET_NCHW, dt, batch_size, channels,
-                                      height, width, rois.size(0), pooled_height, pooled_width,
-                                      spatial_scale, (int)sampling_ratio, aligned, 1, cur_stream()),
-           "roi_align_backward_kernel");
+  auto run = [&](int flags) {
+    return b200det_roi_align_backward(grad.data_ptr(), gs, rois_.data_ptr(), grad_input.data_ptr(),
+                                      nhwc ? B200DET_NHWC : B200DET_NCHW, dt, batch_size, channels, height,
+                                      width, rois.size(0), pooled_height, pooled_width, spatial_scale,
+                                      (int)sampling_ratio, aligned, flags, cur_stream());
+  };
+  // torch.use_deterministic_algorithms(True): the tile-accumulating kernel is bitwise
+  // reproducible; only where it does not apply does the reference's alert fire (:440)
+  if (at::globalContext().deterministicAlgorithms()) {
+    const int rc = run(B200DET_BWD_ZERO_INIT | B200DET_BWD_DETERMINISTIC);
+    if (rc == 0) return grad_input;
+    TORCH_CHECK(rc == B200DET_ENOSUP, "roi_align_backward_kernel failed (", rc, "): ", b200det_last_error());
+  }
+  at::globalContext().alertNotDeterministic("roi_align_backward_kernel");
+  check_rc(run(B200DET_BWD_ZERO_INIT), "roi_align_backward_kernel");
   return grad_input;
 }
 
@@ -241,7 +250,6 @@ std::vector<at::Tensor> msroi_align_backward_cuda(
   check_roi_dtype(grad, rois, "msroi_align_backward");
   at::cuda::CUDAGuard device_guard(grad.device());
   const int dt = dtype_code(grad.scalar_type(), "msroi_align_backward");
-  at::globalContext().alertNotDeterministic("msroi_align_backward");
   std::vector<at::Tensor> out(L);
   void* ptrs[B200DET_MAX_LEVELS];
   int64_t hs[B200DET_MAX_LEVELS], ws[B200DET_MAX_LEVELS];
@@ -258,12 +266,19 @@ std::vector<at::Tensor> msroi_align_backward_cuda(
   const at::Tensor rois_ = arith_rois(rois, grad.scalar_type());
   const at::Tensor levels_ = levels.to(at::kInt).contiguous();
   const int64_t gs[4] = {grad.stride(0), grad.stride(1), grad.stride(2), grad.stride(3)};
-  check_rc(b200det_msroi_align_backward(grad.data_ptr(), gs, rois_.data_ptr(),
-                                        levels_.data_ptr<int32_t>(), ptrs, hs, ws, sc, L,
-                                        channels_last ? B200DET_NHWC : B200DET_NCHW, dt, batch_size,
-                                        channels, rois.size(0), pooled_height, pooled_width,
-                                        (int)sampling_ratio, aligned, 1, cur_stream()),
-           "msroi_align_backward");
+  auto run = [&](int flags) {
+    return b200det_msroi_align_backward(grad.data_ptr(), gs, rois_.data_ptr(), levels_.data_ptr<int32_t>(), ptrs,
+                                        hs, ws, sc, L, channels_last ? B200DET_NHWC : B200DET_NCHW, dt,
+                                        batch_size, channels, rois.size(0), pooled_height, pooled_width,
+                                        (int)sampling_ratio, aligned, flags, cur_stream());
+  };
+  if (at::globalContext().deterministicAlgorithms()) {
+    const int rc = run(B200DET_BWD_ZERO_INIT | B200DET_BWD_DETERMINISTIC);
+    if (rc == 0) return out;
+    TORCH_CHECK(rc == B200DET_ENOSUP, "msroi_align_backward failed (", rc, "): ", b200det_last_error());
+  }
+  at::globalContext().alertNotDeterministic("msroi_align_backward");
+  check_rc(run(B200DET_BWD_ZERO_INIT), "msroi_align_backward");
   return out;
 }
 

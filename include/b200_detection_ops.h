@@ -84,14 +84,23 @@ int b200det_roi_align_forward(
  *   grad         : device, logical [K, C, PH, PW] with ARBITRARY element
  *                  strides grad_strides[4] = (k, c, ph, pw), as the reference
  *                  honours (:253-256, :435-438)
- *   grad_input   : device, logical [N, C, H, W] in `gi_layout`; zero-filled
- *                  by this call when zero_init != 0, then accumulated into
- *                  with red.global.add (non-deterministic order, as :440). */
+ *   grad_input   : device, logical [N, C, H, W] in `gi_layout`
+ *   flags        : B200DET_BWD_ZERO_INIT  zero-fill grad_input in this call (fused
+ *                    with the scatter; the reference's at::zeros, :427) -- without
+ *                    it the call accumulates into what is there;
+ *                  B200DET_BWD_DETERMINISTIC  use the tile-accumulating kernel
+ *                    (no atomics, fixed summation order: bitwise reproducible;
+ *                    channels_last, C % 128 == 0, sampling_ratio 1 or 2 only,
+ *                    B200DET_ENOSUP otherwise).  Without it gradients are
+ *                    accumulated with red.global.add in non-deterministic order,
+ *                    like the reference (:440). */
+#define B200DET_BWD_ZERO_INIT 1
+#define B200DET_BWD_DETERMINISTIC 2
 int b200det_roi_align_backward(
     const void* grad, const int64_t* grad_strides, const void* rois,
     void* grad_input, int gi_layout, int dtype, int64_t N, int64_t C,
     int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
-    double spatial_scale, int sampling_ratio, int aligned, int zero_init,
+    double spatial_scale, int sampling_ratio, int aligned, int flags,
     void* stream);
 
 /* FPN level mapper.  Replaces LevelMapper.__call__
@@ -127,14 +136,14 @@ int b200det_msroi_align_forward(
 
 /* MultiScaleRoIAlign backward: the autograd transpose of the call above.
  *   grad_feats[l] : device, logical [N, C, heights[l], widths[l]] in `layout`,
- *                   zero-filled here when zero_init != 0
+ *                   (flags as in b200det_roi_align_backward)
  *   levels        : device int32 [K], as produced by the forward */
 int b200det_msroi_align_backward(
     const void* grad, const int64_t* grad_strides, const void* rois,
     const int32_t* levels, void* const* grad_feats, const int64_t* heights,
     const int64_t* widths, const double* scales, int num_levels, int layout,
     int dtype, int64_t N, int64_t C, int64_t K, int64_t PH, int64_t PW,
-    int sampling_ratio, int aligned, int zero_init, void* stream);
+    int sampling_ratio, int aligned, int flags, void* stream);
 
 /* ------------------------------------------------------------------------
  * NMS

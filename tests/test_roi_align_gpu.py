@@ -372,3 +372,78 @@ def test_cfg3_full_size_levels_and_adjoint(capi, dtype):
         close_fwd(got, want)
     else:
         torch.testing.assert_close(got, want.to(dtype).float(), rtol=1e-2, atol=1e-2)
+
+
+# ------------------------------------------------------------------ backward variants (C-ABI flags)
+def _bwd_case(seed, N=3, C=256, H=40, W=56, K=200, PH=7, scale=0.25, lo=8.0, sort=True):
+    g = torch.Generator().manual_seed(seed)
+    rois = rand_rois(g, K, N, W / scale, H / scale, lo=lo)
+    if not sort:
+        rois = rois[torch.randperm(K, generator=g)]
+    go = torch.randn(K, C, PH, PH, generator=g)
+    want64 = oracle.roi_align_backward(go.double(), rois.double(), scale, PH, PH, N, C, H, W, 2, False)
+    return rois, go, want64, (N, C, H, W, PH, scale)
+
+
+@pytest.mark.parametrize("ph,scale,lo", [(7, 0.25, 8.0), (14, 0.25, 16.0), (7, 0.0625, 4.0)])
+def test_backward_deterministic_tile_kernel(capi, ph, scale, lo):
+    """B200DET_BWD_DETERMINISTIC: tile accumulation, no atomics -- bitwise reproducible and equal to the
+    fp64 oracle within fp32 rounding (the role of ops/roi_align.py:251-255 in the reference)."""
+    rois, go, want64, (N, C, H, W, PH, sc) = _bwd_case(11 + ph, PH=ph, scale=scale, lo=lo)
+    god = go.to(DEV).contiguous(memory_format=torch.channels_last)
+    runs = [capi.roi_align_backward(god, rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False, layout=capi.NHWC,
+                                    deterministic=True) for _ in range(3)]
+    close_bwd(runs[0], want64)
+    assert torch.equal(runs[0], runs[1]) and torch.equal(runs[0], runs[2])
+    # bf16 I/O, fp32 accumulation in shared memory: one rounding at the end, much tighter than packed atomics
+    gb = capi.roi_align_backward(god.to(torch.bfloat16), rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False,
+                                 layout=capi.NHWC, deterministic=True)
+    want_b = oracle.roi_align_backward(go.to(torch.bfloat16).double(), rois.double(), sc, PH, PH, N, C, H, W, 2, False)
+    close_bwd(gb.float(), want_b, rtol=1e-2)
+    # not available for NCHW: the call must say so instead of silently using atomics
+    with pytest.raises(RuntimeError):
+        capi.roi_align_backward(go.to(DEV), rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False, layout=capi.NCHW,
+                                deterministic=True)
+
+
+@pytest.mark.parametrize("deterministic", [False, True])
+def test_backward_rois_not_grouped_by_image(capi, deterministic):
+    """Tensor[K,5] rois may come in any order (roi_align_kernel.cu:90 just reads the batch index)."""
+    rois, go, want64, (N, C, H, W, PH, sc) = _bwd_case(5, sort=False)
+    assert not bool((rois[1:, 0] >= rois[:-1, 0]).all())
+    god = go.to(DEV).contiguous(memory_format=torch.channels_last)
+    gi = capi.roi_align_backward(god, rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False, layout=capi.NHWC,
+                                 deterministic=deterministic)
+    close_bwd(gi, want64)
+
+
+@pytest.mark.parametrize("deterministic", [False, True])
+def test_backward_accumulates_without_zero_init(capi, deterministic):
+    rois, go, want64, (N, C, H, W, PH, sc) = _bwd_case(6)
+    g = torch.Generator().manual_seed(60)
+    base = torch.randn(N, C, H, W, generator=g)
+    out = base.to(DEV).contiguous(memory_format=torch.channels_last)
+    god = go.to(DEV).contiguous(memory_format=torch.channels_last)
+    gi = capi.roi_align_backward(god, rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False, layout=capi.NHWC, out=out,
+                                 zero_init=False, deterministic=deterministic)
+    assert gi.data_ptr() == out.data_ptr()
+    close_bwd(gi, want64 + base.double())
+
+
+def test_deterministic_mode_through_the_dispatcher():
+    """torch.use_deterministic_algorithms(True): channels_last gradients take the tile kernel (no error, bitwise
+    equal runs); NCHW ones raise like the reference's alertNotDeterministic (roi_align_kernel.cu:440)."""
+    import cpu_vision_b200  # noqa: F401
+
+    rois, go, want64, (N, C, H, W, PH, sc) = _bwd_case(7)
+    god = go.to(DEV).contiguous(memory_format=torch.channels_last)
+    torch.use_deterministic_algorithms(True)
+    try:
+        a = torch.ops.torchvision._roi_align_backward(god, rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False)
+        b = torch.ops.torchvision._roi_align_backward(god, rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False)
+        assert torch.equal(a, b)
+        close_bwd(a, want64)
+        with pytest.raises(RuntimeError):
+            torch.ops.torchvision._roi_align_backward(go.to(DEV), rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False)
+    finally:
+        torch.use_deterministic_algorithms(False)
