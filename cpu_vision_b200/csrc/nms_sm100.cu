@@ -166,11 +166,141 @@ __global__ void __launch_bounds__(kTile) nms_mask_kernel(int n, float thr,
 }
 
 // ---- 5. greedy scan -----------------------------------------------------------
-// One CTA walks the 64-box blocks in score order.  remv[] (one bit per box)
-// lives in shared memory; for block b thread 0 resolves the 64 in-block
-// decisions from the diagonal words, then all threads OR the kept rows into
-// the words to the right.  Finally the kept bits are compacted into keep[].
+// One CTA walks the 64-box blocks in score order; remv[] (one bit per box) lives in
+// shared memory.  Per block: (a) one thread resolves the 64 in-block decisions from
+// the diagonal words -- all 64 words are loaded up front, the dependent chain is a
+// predicated AND per box; a box that is alive when visited is kept and is never
+// cleared later (its row only has bits to its right), so kept == the final alive
+// word; (b) all threads OR the kept rows into the words to the right.  Finally the
+// kept bits are compacted into keep[].
+//
+// nms_scan_smem_kernel (col_blocks <= kSmemBlocks, i.e. N <= 6144 -- the detection
+// sizes): the 64 mask rows of block b+1 are prefetched into shared memory with
+// cp.async while block b is resolved, so no step waits on L2.
+// nms_scan_kernel (any N): rows of kept boxes are read from global memory.
 constexpr int kScanThreads = 1024;
+constexpr int kSmemThreads = 512;
+constexpr int kSmemBlocks = 96;
+
+__device__ __forceinline__ u64 resolve_block(u64 alive, const u64* __restrict__ diag, int stride) {
+  u64 d[kTile];
+#pragma unroll
+  for (int i = 0; i < kTile; ++i) d[i] = diag[(size_t)i * stride];
+#pragma unroll
+  for (int i = 0; i < kTile; ++i)
+    if ((alive >> i) & 1ULL) alive &= ~d[i];
+  return alive;
+}
+
+// compaction of the kept bits: running offset over words, blockDim.x words per pass
+__device__ __forceinline__ void compact_keep(const u64* keptw, int col_blocks, const int32_t* __restrict__ order,
+                                             int64_t* __restrict__ keep, int64_t* __restrict__ num_keep,
+                                             int* s_base, u64* s_total) {
+  const int tid = threadIdx.x, nthreads = blockDim.x, nwarps = nthreads >> 5;
+  int running = 0;
+  for (int w0 = 0; w0 < col_blocks; w0 += nthreads) {
+    const int w = w0 + tid;
+    const u64 kw = w < col_blocks ? keptw[w] : 0ULL;
+    const int cnt = __popcll(kw);
+    int incl = cnt;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((tid & 31) >= o) incl += v;
+    }
+    if ((tid & 31) == 31) s_base[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+      const int v = tid < nwarps ? s_base[tid] : 0;
+      int inc2 = v;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, inc2, o);
+        if (tid >= o) inc2 += u;
+      }
+      s_base[tid] = inc2 - v;  // exclusive
+      if (tid == 31) *s_total = (u64)inc2;
+    }
+    __syncthreads();
+    int pos = running + s_base[tid >> 5] + incl - cnt;
+    u64 kk = kw;
+    while (kk) {
+      const int i = __ffsll((long long)kk) - 1;
+      kk &= kk - 1;
+      keep[pos++] = (int64_t)order[w * kTile + i];
+    }
+    running += (int)*s_total;
+    __syncthreads();
+  }
+  if (tid == 0) *num_keep = running;
+}
+
+__global__ void __launch_bounds__(kSmemThreads) nms_scan_smem_kernel(
+    const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
+    int64_t* __restrict__ keep, int64_t* __restrict__ num_keep) {
+  extern __shared__ u64 smem[];
+  u64* remv = smem;                     // [col_blocks]
+  u64* keptw = smem + col_blocks;       // [col_blocks]
+  u64* stage = smem + 2 * col_blocks;   // [2][kTile * col_blocks]
+  __shared__ u64 s_kept;
+  __shared__ int s_base[32];
+  const int tid = threadIdx.x;
+  for (int j = tid; j < col_blocks; j += kSmemThreads) remv[j] = 0;
+
+  auto prefetch = [&](int b) {  // words j >= b of the rows of block b; a warp copies whole rows
+    u64* dst = stage + (size_t)(b & 1) * kTile * col_blocks;
+    const int rows = min(n - b * kTile, kTile);
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int i = warp; i < rows; i += kSmemThreads / 32) {
+      const u64* src = mask + (size_t)(b * kTile + i) * col_blocks;
+      u64* d = dst + i * col_blocks;
+      for (int j = b + lane; j < col_blocks; j += 32) {
+        const unsigned sa = (unsigned)__cvta_generic_to_shared(d + j);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(src + j) : "memory");
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  prefetch(0);
+  for (int b = 0; b < col_blocks; ++b) {
+    if (b + 1 < col_blocks) {
+      prefetch(b + 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const u64* rowsb = stage + (size_t)(b & 1) * kTile * col_blocks;
+    const int rows = min(n - b * kTile, kTile);
+    if (tid == 0) {
+      u64 alive = ~remv[b];
+      if (rows < kTile) alive &= (1ULL << rows) - 1ULL;
+      // rows >= `rows` of the stage hold stale data, but their alive bits are clear
+      const u64 kept = resolve_block(alive, rowsb + b, col_blocks);
+      s_kept = kept;
+      keptw[b] = kept;
+    }
+    __syncthreads();
+    // OR the kept rows into the words to the right: 4 thread groups take 16 rows each, branch-free
+    const u64 kept = s_kept;
+    {
+      constexpr int kPer = kSmemThreads / 4;
+      const int q = tid / kPer;
+      const unsigned kq = (unsigned)(kept >> (16 * q)) & 0xffffu;
+      if (kq)
+        for (int j = b + 1 + (tid - q * kPer); j < col_blocks; j += kPer) {
+          const u64* col = rowsb + (size_t)(16 * q) * col_blocks + j;
+          u64 acc = 0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const u64 v = col[(size_t)i * col_blocks];
+            acc |= ((kq >> i) & 1u) ? v : 0ULL;
+          }
+          if (acc) atomicOr(remv + j, acc);
+        }
+    }
+    __syncthreads();  // stage (b & 1) is refilled by the prefetch of block b + 2
+  }
+  compact_keep(keptw, col_blocks, order, keep, num_keep, s_base, &s_kept);
+}
 
 __global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
@@ -192,14 +322,7 @@ __global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
     if (tid == 0) {
       u64 alive = ~remv[b];
       if (rows < kTile) alive &= (1ULL << rows) - 1ULL;
-      u64 kept = 0;
-#pragma unroll
-      for (int i = 0; i < kTile; ++i) {
-        if ((alive >> i) & 1ULL) {
-          kept |= 1ULL << i;
-          alive &= ~diag[i];
-        }
-      }
+      const u64 kept = resolve_block(alive, diag, 1);
       s_kept = kept;
       keptw[b] = kept;
     }
@@ -217,43 +340,7 @@ __global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
     }
     __syncthreads();
   }
-
-  // compaction: running offset over words, kScanThreads words per pass
-  int running = 0;
-  for (int w0 = 0; w0 < col_blocks; w0 += kScanThreads) {
-    const int w = w0 + tid;
-    const u64 kw = w < col_blocks ? keptw[w] : 0ULL;
-    const int cnt = __popcll(kw);
-    // block exclusive scan of cnt
-    int incl = cnt;
-    for (int o = 1; o < 32; o <<= 1) {
-      const int v = __shfl_up_sync(0xffffffffu, incl, o);
-      if ((tid & 31) >= o) incl += v;
-    }
-    if ((tid & 31) == 31) s_base[tid >> 5] = incl;
-    __syncthreads();
-    if (tid < 32) {
-      int v = tid < kScanThreads / 32 ? s_base[tid] : 0;
-      int inc2 = v;
-      for (int o = 1; o < 32; o <<= 1) {
-        const int u = __shfl_up_sync(0xffffffffu, inc2, o);
-        if (tid >= o) inc2 += u;
-      }
-      s_base[tid] = inc2 - v;  // exclusive
-      if (tid == 31) s_kept = (u64)inc2;  // pass total
-    }
-    __syncthreads();
-    int pos = running + s_base[tid >> 5] + incl - cnt;
-    u64 kk = kw;
-    while (kk) {
-      const int i = __ffsll((long long)kk) - 1;
-      kk &= kk - 1;
-      keep[pos++] = (int64_t)order[w * kTile + i];
-    }
-    running += (int)s_kept;
-    __syncthreads();
-  }
-  if (tid == 0) *num_keep = running;
+  compact_keep(keptw, col_blocks, order, keep, num_keep, s_base, &s_kept);
 }
 
 __global__ void nms_zero_count_kernel(int64_t* num_keep) { *num_keep = 0; }
@@ -334,10 +421,17 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
   dim3 grid(col_blocks, col_blocks);
   nms_mask_kernel<BoxT><<<grid, kTile, 0, st>>>((int)n, (float)thr, (const BoxT*)L.sorted,
                                                mode == 2 ? L.cls : nullptr, L.mask);
-  const size_t smem = (size_t)col_blocks * 16;
-  if (smem > 48 * 1024)
-    B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  nms_scan_kernel<<<1, kScanThreads, smem, st>>>(L.mask, (int)n, col_blocks, L.order, keep, num_keep);
+  if (col_blocks <= kSmemBlocks) {
+    const size_t smem = ((size_t)2 * col_blocks + (size_t)2 * kTile * col_blocks) * sizeof(u64);
+    if (smem > 48 * 1024)
+      B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    nms_scan_smem_kernel<<<1, kSmemThreads, smem, st>>>(L.mask, (int)n, col_blocks, L.order, keep, num_keep);
+  } else {
+    const size_t smem = (size_t)col_blocks * 16;
+    if (smem > 48 * 1024)
+      B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    nms_scan_kernel<<<1, kScanThreads, smem, st>>>(L.mask, (int)n, col_blocks, L.order, keep, num_keep);
+  }
   B200DET_CUDA_OK(cudaGetLastError());
   return 0;
 }
