@@ -295,12 +295,21 @@ def run_b200(args, rank, world, local):
     out_bytes = K * C * ph * ph * es
     algo = {"fwd": feat_bytes + out_bytes + K * 20, "bwd": out_bytes + feat_bytes + K * 20}
     peak, peak_src = measured_peak()
+    # DRAM bytes of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json,
+    # written by hand from profiles/*.ncu.txt after each capture); null when no capture matches
+    traffic = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(args.workload, {})
+    except Exception:
+        pass
     dom = "bwd" if bwd_ms >= fwd_ms else "fwd"
     dom_ms = bwd_ms if dom == "bwd" else fwd_ms
     achieved = algo[dom] / (dom_ms / 1e3) / 1e9
     roofline = {
         "bound": "hbm", "kernel": f"msroi_align_{dom}", "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": algo[dom],
+        "frac": achieved / peak, "traffic": traffic.get(dom), "traffic_source": traffic.get("source"),
+        "peak_source": peak_src, "algorithmic_bytes_per_launch": algo[dom],
         "fwd": {"ms": fwd_ms, "GBps": algo["fwd"] / (fwd_ms / 1e3) / 1e9, "frac": algo["fwd"] / (fwd_ms / 1e3) / 1e9 / peak},
         "bwd": {"ms": bwd_ms, "GBps": algo["bwd"] / (bwd_ms / 1e3) / 1e9, "frac": algo["bwd"] / (bwd_ms / 1e3) / 1e9 / peak},
         "fwd_bwd_frac": (algo["fwd"] + algo["bwd"]) / (ms_per_step / 1e3) / 1e9 / peak,

@@ -5,8 +5,10 @@
 // runs the device entry points of c_api.cu on a private stream and copies the
 // results back before returning.  Pinned caller buffers get full PCIe rate;
 // pageable ones work at whatever cudaMemcpyAsync's internal staging gives.
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -14,9 +16,16 @@
 namespace b200det {
 namespace {
 
+constexpr int kMaxChunks = 16;
+
 struct Arena {
   int device = -1;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;      // kernels
+  cudaStream_t s_in = nullptr;        // host -> device copies of the chunked entry points
+  cudaStream_t s_out = nullptr;       // device -> host copies
+  cudaEvent_t ev_in[kMaxChunks] = {}, ev_k[kMaxChunks] = {};
+  void* stage = nullptr;              // pinned scratch (rebased RoIs)
+  size_t stage_cap = 0;
   void* buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   size_t cap[6] = {0, 0, 0, 0, 0, 0};
   void* pinned = nullptr;  // small bounce buffer for counts
@@ -25,17 +34,74 @@ struct Arena {
 Arena g_arena;
 std::mutex g_mu;
 
+void arena_destroy_aux() {
+  if (g_arena.s_in) cudaStreamDestroy(g_arena.s_in);
+  if (g_arena.s_out) cudaStreamDestroy(g_arena.s_out);
+  for (int i = 0; i < kMaxChunks; ++i) {
+    if (g_arena.ev_in[i]) cudaEventDestroy(g_arena.ev_in[i]);
+    if (g_arena.ev_k[i]) cudaEventDestroy(g_arena.ev_k[i]);
+  }
+  if (g_arena.stage) cudaFreeHost(g_arena.stage);
+}
+
+int stage_get(size_t bytes, void** out) {
+  if (g_arena.stage_cap < bytes) {
+    if (g_arena.stage) B200DET_CUDA_OK(cudaFreeHost(g_arena.stage));
+    g_arena.stage = nullptr;
+    g_arena.stage_cap = 0;
+    B200DET_CUDA_OK(cudaMallocHost(&g_arena.stage, bytes + bytes / 4 + 4096));
+    g_arena.stage_cap = bytes + bytes / 4 + 4096;
+  }
+  *out = g_arena.stage;
+  return 0;
+}
+
+// First RoI of every image when the rows are grouped by ascending, in-range image index
+// (convert_boxes_to_roi_format order, ops/_utils.py:18-25); false otherwise.
+bool image_starts(const void* rois, int dtype, int64_t K, int64_t N, std::vector<int64_t>& start) {
+  start.assign((size_t)N + 1, K);
+  int64_t prev = -1;
+  for (int64_t k = 0; k < K; ++k) {
+    const double bd = dtype == B200DET_F64 ? ((const double*)rois)[k * 5] : (double)((const float*)rois)[k * 5];
+    const int64_t b = (int64_t)bd;
+    if (b < 0 || b >= N || b < prev) return false;
+    for (int64_t i = prev + 1; i <= b; ++i) start[(size_t)i] = k;
+    prev = b;
+  }
+  return true;
+}
+
+// how many image chunks the host entry points pipeline over (H2D of chunk c+1, kernels of chunk c and
+// D2H of chunk c-1 overlap; PCIe is full duplex).  B200DET_HOST_CHUNKS overrides (1 = no pipelining).
+int host_chunks(int64_t N) {
+  static int env = -1;
+  if (env < 0) {
+    const char* e = getenv("B200DET_HOST_CHUNKS");
+    env = e ? atoi(e) : 16;
+    if (env < 1) env = 1;
+    if (env > kMaxChunks) env = kMaxChunks;
+  }
+  return (int)(N < env ? (N > 0 ? N : 1) : env);
+}
+
 int arena_bind(int device) {
   if (g_arena.device != device) {
     if (g_arena.device >= 0) {
       cudaSetDevice(g_arena.device);
       for (int i = 0; i < 6; ++i) { if (g_arena.buf[i]) cudaFree(g_arena.buf[i]); g_arena.buf[i] = nullptr; g_arena.cap[i] = 0; }
+      arena_destroy_aux();
       if (g_arena.stream) cudaStreamDestroy(g_arena.stream);
       if (g_arena.pinned) cudaFreeHost(g_arena.pinned);
       g_arena = Arena();
     }
     B200DET_CUDA_OK(cudaSetDevice(device));
     B200DET_CUDA_OK(cudaStreamCreateWithFlags(&g_arena.stream, cudaStreamNonBlocking));
+    B200DET_CUDA_OK(cudaStreamCreateWithFlags(&g_arena.s_in, cudaStreamNonBlocking));
+    B200DET_CUDA_OK(cudaStreamCreateWithFlags(&g_arena.s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < kMaxChunks; ++i) {
+      B200DET_CUDA_OK(cudaEventCreateWithFlags(&g_arena.ev_in[i], cudaEventDisableTiming));
+      B200DET_CUDA_OK(cudaEventCreateWithFlags(&g_arena.ev_k[i], cudaEventDisableTiming));
+    }
     B200DET_CUDA_OK(cudaMallocHost(&g_arena.pinned, 256));
     g_arena.device = device;
   } else {
@@ -153,28 +219,51 @@ int b200det_msroi_align_forward_host(const void* const* feats, const int64_t* he
   if (rc) return rc;
   size_t off[B200DET_MAX_LEVELS];
   const size_t feat_b = level_offsets(heights, widths, num_levels, N, C, es, off);
-  const size_t roi_b = (size_t)K * 5 * (dtype == B200DET_F64 ? 8 : 4),
-               out_b = (size_t)K * C * PH * PW * es;
+  const size_t res = dtype == B200DET_F64 ? 8 : 4;
+  const size_t roi_b = (size_t)K * 5 * res, row_b = (size_t)C * PH * PW * es, out_b = (size_t)K * row_b;
   void *d_feat, *d_roi, *d_out, *d_lv;
   if ((rc = arena_get(0, feat_b, &d_feat)) || (rc = arena_get(1, roi_b, &d_roi)) ||
       (rc = arena_get(2, out_b, &d_out)) || (rc = arena_get(3, (size_t)K * 4, &d_lv)))
     return rc;
-  cudaStream_t st = g_arena.stream;
+  cudaStream_t st = g_arena.stream, s_in = g_arena.s_in, s_out = g_arena.s_out;
   const void* d_ptrs[B200DET_MAX_LEVELS];
+  for (int l = 0; l < num_levels; ++l) d_ptrs[l] = (char*)d_feat + off[l];
   if (roi_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_roi, rois, roi_b, cudaMemcpyHostToDevice, st));
-  for (int l = 0; l < num_levels; ++l) {
-    d_ptrs[l] = (char*)d_feat + off[l];
-    const size_t b = (size_t)N * C * heights[l] * widths[l] * es;
-    if (b) B200DET_CUDA_OK(cudaMemcpyAsync((void*)d_ptrs[l], feats[l], b, cudaMemcpyHostToDevice, st));
+
+  // Pipeline over image chunks: the features of chunk c+1 go up while chunk c is pooled and the
+  // pooled rows of chunk c-1 go down.  Needs RoIs grouped by image; otherwise one chunk.
+  std::vector<int64_t> start;
+  int chunks = host_chunks(N);
+  if (chunks > 1 && (!rois || !image_starts(rois, dtype, K, N, start))) chunks = 1;
+  if (chunks <= 1) start.assign((size_t)N + 1, K), start[0] = 0;
+  for (int c = 0; c < chunks; ++c) {
+    const int64_t i0 = N * c / chunks, i1 = N * (c + 1) / chunks;
+    const int64_t k0 = chunks > 1 ? start[(size_t)i0] : 0, k1 = chunks > 1 ? start[(size_t)i1] : K;
+    for (int l = 0; l < num_levels; ++l) {
+      const size_t img_b = (size_t)C * heights[l] * widths[l] * es;
+      if (img_b && i1 > i0)
+        B200DET_CUDA_OK(cudaMemcpyAsync((char*)d_ptrs[l] + i0 * img_b, (const char*)feats[l] + i0 * img_b,
+                                        (size_t)(i1 - i0) * img_b, cudaMemcpyHostToDevice, s_in));
+    }
+    B200DET_CUDA_OK(cudaEventRecord(g_arena.ev_in[c], s_in));
+    B200DET_CUDA_OK(cudaStreamWaitEvent(st, g_arena.ev_in[c], 0));
+    if (k1 > k0) {
+      rc = b200det_msroi_align_forward(d_ptrs, heights, widths, scales, num_levels, layout,
+                                       (const char*)d_roi + k0 * 5 * res, (int32_t*)d_lv + k0, 0,
+                                       (char*)d_out + k0 * row_b, out_layout, dtype, N, C, k1 - k0, PH, PW,
+                                       sampling_ratio, aligned, k_min, k_max, canonical_scale, canonical_level,
+                                       eps, st);
+      if (rc) return rc;
+    }
+    B200DET_CUDA_OK(cudaEventRecord(g_arena.ev_k[c], st));
+    B200DET_CUDA_OK(cudaStreamWaitEvent(s_out, g_arena.ev_k[c], 0));
+    if (k1 > k0 && row_b)
+      B200DET_CUDA_OK(cudaMemcpyAsync((char*)output + k0 * row_b, (char*)d_out + k0 * row_b,
+                                      (size_t)(k1 - k0) * row_b, cudaMemcpyDeviceToHost, s_out));
   }
-  rc = b200det_msroi_align_forward(d_ptrs, heights, widths, scales, num_levels, layout, d_roi,
-                                   (int32_t*)d_lv, 0, d_out, out_layout, dtype, N, C, K, PH, PW,
-                                   sampling_ratio, aligned, k_min, k_max, canonical_scale,
-                                   canonical_level, eps, st);
-  if (rc) return rc;
-  if (out_b) B200DET_CUDA_OK(cudaMemcpyAsync(output, d_out, out_b, cudaMemcpyDeviceToHost, st));
   if (levels && K && num_levels > 1)
-    B200DET_CUDA_OK(cudaMemcpyAsync(levels, d_lv, (size_t)K * 4, cudaMemcpyDeviceToHost, st));
+    B200DET_CUDA_OK(cudaMemcpyAsync(levels, d_lv, (size_t)K * 4, cudaMemcpyDeviceToHost, s_out));
+  B200DET_CUDA_OK(cudaStreamSynchronize(s_out));
   B200DET_CUDA_OK(cudaStreamSynchronize(st));
   if (levels && num_levels == 1) memset(levels, 0, (size_t)K * 4);
   return 0;
@@ -196,30 +285,81 @@ int b200det_msroi_align_backward_host(const void* grad, const int64_t* grad_stri
     return fail(B200DET_EINVAL, "msroi_align_backward_host: negative size");
   if (num_levels > 1 && K > 0 && !levels)
     return fail(B200DET_EINVAL, "msroi_align_backward_host: levels required");
+  if (K > 0 && (!grad || !grad_strides || !rois))
+    return fail(B200DET_EINVAL, "msroi_align_backward_host: null pointer");
   int rc = arena_bind(device);
   if (rc) return rc;
   size_t off[B200DET_MAX_LEVELS];
   const size_t feat_b = level_offsets(heights, widths, num_levels, N, C, es, off);
-  const size_t roi_b = (size_t)K * 5 * (dtype == B200DET_F64 ? 8 : 4),
-               g_b = (size_t)grad_span_elems * es;
+  const size_t res = dtype == B200DET_F64 ? 8 : 4;
+  const size_t roi_b = (size_t)K * 5 * res, g_b = (size_t)grad_span_elems * es;
   void *d_feat, *d_roi, *d_g, *d_lv;
   if ((rc = arena_get(0, feat_b, &d_feat)) || (rc = arena_get(1, roi_b, &d_roi)) ||
       (rc = arena_get(2, g_b, &d_g)) || (rc = arena_get(3, (size_t)K * 4, &d_lv)))
     return rc;
-  cudaStream_t st = g_arena.stream;
-  void* d_ptrs[B200DET_MAX_LEVELS];
+  cudaStream_t st = g_arena.stream, s_in = g_arena.s_in, s_out = g_arena.s_out;
+  char* d_ptrs[B200DET_MAX_LEVELS];
   for (int l = 0; l < num_levels; ++l) d_ptrs[l] = (char*)d_feat + off[l];
-  if (roi_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_roi, rois, roi_b, cudaMemcpyHostToDevice, st));
+
+  // Pipeline over image chunks (see the forward).  Needs RoIs grouped by image and a gradient whose
+  // rows are laid out one after the other (stride of k = size of a row block); otherwise one chunk.
+  std::vector<int64_t> start;
+  int chunks = host_chunks(N);
+  const bool rows_dense = K > 0 && grad_strides[0] > 0 && grad_strides[0] * K == grad_span_elems;
+  if (chunks > 1 && (!rows_dense || !image_starts(rois, dtype, K, N, start))) chunks = 1;
   if (levels && K) B200DET_CUDA_OK(cudaMemcpyAsync(d_lv, levels, (size_t)K * 4, cudaMemcpyHostToDevice, st));
-  if (g_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_g, grad, g_b, cudaMemcpyHostToDevice, st));
-  rc = b200det_msroi_align_backward(d_g, grad_strides, d_roi, (const int32_t*)d_lv, d_ptrs, heights,
-                                    widths, scales, num_levels, layout, dtype, N, C, K, PH, PW,
-                                    sampling_ratio, aligned, 1, st);
-  if (rc) return rc;
-  for (int l = 0; l < num_levels; ++l) {
-    const size_t b = (size_t)N * C * heights[l] * widths[l] * es;
-    if (b) B200DET_CUDA_OK(cudaMemcpyAsync(grad_feats[l], d_ptrs[l], b, cudaMemcpyDeviceToHost, st));
+  if (chunks <= 1) {
+    if (roi_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_roi, rois, roi_b, cudaMemcpyHostToDevice, st));
+    if (g_b) B200DET_CUDA_OK(cudaMemcpyAsync(d_g, grad, g_b, cudaMemcpyHostToDevice, st));
+    rc = b200det_msroi_align_backward(d_g, grad_strides, d_roi, (const int32_t*)d_lv, (void* const*)d_ptrs,
+                                      heights, widths, scales, num_levels, layout, dtype, N, C, K, PH, PW,
+                                      sampling_ratio, aligned, B200DET_BWD_ZERO_INIT, st);
+    if (rc) return rc;
+    for (int l = 0; l < num_levels; ++l) {
+      const size_t b = (size_t)N * C * heights[l] * widths[l] * es;
+      if (b) B200DET_CUDA_OK(cudaMemcpyAsync(grad_feats[l], d_ptrs[l], b, cudaMemcpyDeviceToHost, st));
+    }
+    B200DET_CUDA_OK(cudaStreamSynchronize(st));
+    return 0;
   }
+  // each chunk is a call on its own images: batch indices rebased to the chunk (pinned staging copy)
+  void* h_roi;
+  if ((rc = stage_get(roi_b, &h_roi))) return rc;
+  memcpy(h_roi, rois, roi_b);
+  for (int c = 0; c < chunks; ++c) {
+    const int64_t i0 = N * c / chunks;
+    for (int64_t k = start[(size_t)i0]; k < start[(size_t)(N * (c + 1) / chunks)]; ++k) {
+      if (dtype == B200DET_F64) ((double*)h_roi)[k * 5] -= (double)i0;
+      else ((float*)h_roi)[k * 5] -= (float)i0;
+    }
+  }
+  B200DET_CUDA_OK(cudaMemcpyAsync(d_roi, h_roi, roi_b, cudaMemcpyHostToDevice, st));
+  const size_t gk_b = (size_t)grad_strides[0] * es;
+  for (int c = 0; c < chunks; ++c) {
+    const int64_t i0 = N * c / chunks, i1 = N * (c + 1) / chunks;
+    const int64_t k0 = start[(size_t)i0], k1 = start[(size_t)i1];
+    if (k1 > k0)
+      B200DET_CUDA_OK(cudaMemcpyAsync((char*)d_g + k0 * gk_b, (const char*)grad + k0 * gk_b, (size_t)(k1 - k0) * gk_b,
+                                      cudaMemcpyHostToDevice, s_in));
+    B200DET_CUDA_OK(cudaEventRecord(g_arena.ev_in[c], s_in));
+    B200DET_CUDA_OK(cudaStreamWaitEvent(st, g_arena.ev_in[c], 0));
+    void* c_ptrs[B200DET_MAX_LEVELS];
+    for (int l = 0; l < num_levels; ++l) c_ptrs[l] = d_ptrs[l] + (size_t)i0 * C * heights[l] * widths[l] * es;
+    rc = b200det_msroi_align_backward((char*)d_g + k0 * gk_b, grad_strides, (char*)d_roi + k0 * 5 * res,
+                                      (const int32_t*)d_lv + k0, c_ptrs, heights, widths, scales, num_levels,
+                                      layout, dtype, i1 - i0, C, k1 - k0, PH, PW, sampling_ratio, aligned,
+                                      B200DET_BWD_ZERO_INIT, st);
+    if (rc) return rc;
+    B200DET_CUDA_OK(cudaEventRecord(g_arena.ev_k[c], st));
+    B200DET_CUDA_OK(cudaStreamWaitEvent(s_out, g_arena.ev_k[c], 0));
+    for (int l = 0; l < num_levels; ++l) {
+      const size_t img_b = (size_t)C * heights[l] * widths[l] * es;
+      if (img_b && i1 > i0)
+        B200DET_CUDA_OK(cudaMemcpyAsync((char*)grad_feats[l] + i0 * img_b, (char*)c_ptrs[l], (size_t)(i1 - i0) * img_b,
+                                        cudaMemcpyDeviceToHost, s_out));
+    }
+  }
+  B200DET_CUDA_OK(cudaStreamSynchronize(s_out));
   B200DET_CUDA_OK(cudaStreamSynchronize(st));
   return 0;
 }
@@ -287,6 +427,7 @@ void b200det_host_release(void) {
     g_arena.buf[i] = nullptr;
     g_arena.cap[i] = 0;
   }
+  arena_destroy_aux();
   if (g_arena.stream) cudaStreamDestroy(g_arena.stream);
   if (g_arena.pinned) cudaFreeHost(g_arena.pinned);
   g_arena = Arena();

@@ -447,3 +447,33 @@ def test_deterministic_mode_through_the_dispatcher():
             torch.ops.torchvision._roi_align_backward(go.to(DEV), rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False)
     finally:
         torch.use_deterministic_algorithms(False)
+
+
+@pytest.mark.parametrize("channels_last", [False, True])
+def test_msroi_align_host_entry_points_pipelined(golden, capi, channels_last):
+    """b200det_msroi_align_{forward,backward}_host: CPU tensors in/out, pipelined over image chunks
+    (H2D / kernels / D2H overlap); results must equal the reference fixtures and the device entry points."""
+    d = golden("msroi_align.pt")
+    boxes = d["boxes"]
+    rois = torch.cat([torch.cat([torch.full((len(b), 1), float(i)), b], 1) for i, b in enumerate(boxes)])
+    mf = torch.channels_last if channels_last else torch.contiguous_format
+    layout = capi.NHWC if channels_last else capi.NCHW
+    feats = [f.contiguous(memory_format=mf).pin_memory() for f in d["feats"]]
+    shapes = [tuple(f.shape) for f in feats]
+    assert shapes[0][0] >= 2, "fixture must have several images so that the call really is chunked"
+    out, levels = capi.msroi_align_forward_host(feats, rois, d["scales"], 7, 7, 2, False, d["k_min"], d["k_max"])
+    assert torch.equal(levels.long(), d["levels"])
+    close_fwd(out, d["out_7"])
+    go = d["grad_out_7"].contiguous(memory_format=mf).pin_memory()
+    gis = capi.msroi_align_backward_host(go, rois, levels, d["scales"], shapes, 7, 7, 2, False, layout=layout)
+    for a, b in zip(gis, d["grad_in_7"]):
+        close_bwd(a, b, rtol=2e-5)
+    # RoIs in arbitrary image order: the call falls back to one chunk and must still be right
+    perm = torch.randperm(rois.shape[0], generator=torch.Generator().manual_seed(3))
+    out_p, lv_p = capi.msroi_align_forward_host(feats, rois[perm], d["scales"], 7, 7, 2, False, d["k_min"], d["k_max"])
+    close_fwd(out_p, d["out_7"][perm])
+    gis_p = capi.msroi_align_backward_host(go[perm].contiguous(memory_format=mf), rois[perm], lv_p, d["scales"], shapes,
+                                           7, 7, 2, False, layout=layout)
+    for a, b in zip(gis_p, d["grad_in_7"]):
+        close_bwd(a, b, rtol=2e-5)
+    capi.host_release()
