@@ -51,13 +51,21 @@ struct SegTable {
   int level[kMaxSegs], row0[kMaxSegs], rows[kMaxSegs];
   int first_seg[B200DET_MAX_LEVELS], band_rows[B200DET_MAX_LEVELS], nbands[B200DET_MAX_LEVELS];
   int zfirst[kMaxSegs + 1];             // zero chunks of an image before segment s; [nseg]: per image
+  // levels too big to keep in L2 between fill and scatter are zero-filled up front, all images at once
+  int up_mask;                          // bit l: level l is filled up front
+  int zup;                              // chunks of the up-front fill (numbered before all others)
+  int up_first[B200DET_MAX_LEVELS + 1]; // first up-front chunk of level l
 };
 
 // per-call scheduling state, followed in memory by gid[Kcap], order[Kcap], gsorted[Kcap]
 struct BwdPlan {
+  // the three hot words sit in different 128-byte lines: 2368 warps hammer them
   int task_ctr;                    // next scatter task (global, in group order)
+  int pad0[31];
   int zero_ctr;                    // next zero chunk (global, in group order)
-  int pad[6];
+  int pad1[31];
+  int up_done;                     // up-front chunks finished
+  int pad2[31];
   int zero_done[kMaxGroups];       // per group: chunks finished
   int count[kMaxGroups];           // RoIs of the group
   int start[kMaxGroups + 8];       // exclusive scan of count
@@ -488,6 +496,12 @@ struct BwdArgs {
   SegTable sg;
 };
 
+// pacing reads need no ordering (and ld.acquire costs an L1 invalidation each time)
+__device__ __forceinline__ int ld_relaxed(const int* p) {
+  int v;
+  asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ int ld_acquire(const int* p) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -513,10 +527,20 @@ __device__ __forceinline__ void zero_chunk(const LevelTable<T>& lv, const BwdArg
       if (c < n) { p = reinterpret_cast<char*>(lv.ptr[l]); break; }
       c -= n;
     }
+  } else if (z < a.sg.zup) {
+    g = -1;
+    for (int l = 0; l < lv.num_levels; ++l)
+      if (((a.sg.up_mask >> l) & 1) && z < a.sg.up_first[l + 1]) {
+        c = z - a.sg.up_first[l];
+        bytes = (long long)a.N * lv.sn[l] * (long long)sizeof(T);
+        p = reinterpret_cast<char*>(lv.ptr[l]);
+        break;
+      }
   } else {
     const int cpi = a.sg.zfirst[a.sg.nseg];
-    const int img = z / cpi;
-    c = z - img * cpi;
+    const int zz = z - a.sg.zup;
+    const int img = zz / cpi;
+    c = zz - img * cpi;
     int seg = 0;
     while (seg + 1 < a.sg.nseg && c >= a.sg.zfirst[seg + 1]) ++seg;
     c -= a.sg.zfirst[seg];
@@ -535,7 +559,7 @@ __device__ __forceinline__ void zero_chunk(const LevelTable<T>& lv, const BwdArg
   }
   __threadfence();
   __syncwarp();
-  if (lane == 0) atomicAdd(&a.plan->zero_done[g], 1);
+  if (lane == 0) atomicAdd(g < 0 ? &a.plan->up_done : &a.plan->zero_done[g], 1);
 }
 
 // zero chunks before group g (g may be ngroups: all of them)
@@ -543,7 +567,7 @@ __device__ __forceinline__ int zero_chunks_before(const BwdArgs& a, int g) {
   if (a.ngroups == 1) return g > 0 ? a.ztotal : 0;
   if (g >= a.ngroups) return a.ztotal;
   const int img = g / a.sg.nseg;
-  return img * a.sg.zfirst[a.sg.nseg] + a.sg.zfirst[g - img * a.sg.nseg];
+  return a.sg.zup + img * a.sg.zfirst[a.sg.nseg] + a.sg.zfirst[g - img * a.sg.nseg];
 }
 
 template <typename T, int CH, int SR, int MODE>
@@ -600,13 +624,16 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 4) roi_align_bwd_sm100_kernel(
     if (zeroing) {
       if (done_upto <= g) {
         const int need = zero_chunks_before(a, g + 1);
-        while (claim_zero() + 1 < need) {}  // may take one chunk past `need`: it is wanted anyway
+        while (ld_relaxed(&plan->zero_ctr) < need) claim_zero();
         all_claimed = need >= a.ztotal;
-        if (lane == 0)
+        if (lane == 0) {
+          if (done_upto == 0 && sorted)
+            while (ld_acquire(&plan->up_done) < a.sg.zup) __nanosleep(64);
           for (int q = done_upto; q <= g; ++q) {
             const int n = zero_chunks_before(a, q + 1) - zero_chunks_before(a, q);
             while (ld_acquire(&plan->zero_done[q]) < n) __nanosleep(64);
           }
+        }
         __syncwarp();
         __threadfence();
         done_upto = g + 1;
@@ -616,7 +643,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 4) roi_align_bwd_sm100_kernel(
     if (zeroing && !all_claimed) {
       const int ahead = zero_chunks_before(a, min(g + 1 + a.zlook, a.ngroups));
       for (int i = 0; i < a.zper; ++i) {
-        const int zc = ld_acquire(&plan->zero_ctr);
+        const int zc = ld_relaxed(&plan->zero_ctr);
         all_claimed = zc >= a.ztotal;
         if (zc >= ahead) break;
         claim_zero();
@@ -625,7 +652,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 4) roi_align_bwd_sm100_kernel(
   }
   // whatever the RoIs did not reach (groups without RoIs at the end)
   if (zeroing && !all_claimed)
-    while (ld_acquire(&plan->zero_ctr) < a.ztotal) claim_zero();
+    while (ld_relaxed(&plan->zero_ctr) < a.ztotal) claim_zero();
 }
 
 // ---- host side ---------------------------------------------------------------------------------
@@ -686,13 +713,20 @@ int env_int(const char* name, int dflt) {
   return s ? atoi(s) : dflt;
 }
 
-// cuts every level into bands of at most `budget` bytes per image; false when that needs too many
-bool make_segments(const LevelArgs& lv, size_t es, double budget, SegTable* sg) {
+// Cuts every level whose map (one image) is at most `up_bytes` into bands of at most `budget` bytes; bigger
+// levels are filled up front and their RoIs ride with the image's last segment.  False when nothing is
+// left to segment or it needs too many segments.
+bool make_segments(const LevelArgs& lv, size_t es, double budget, double up_bytes, SegTable* sg) {
   sg->nseg = 0;
+  sg->up_mask = 0;
   for (int li = 0; li < lv.num_levels; ++li) {
     const int l = lv.num_levels - 1 - li;  // coarse levels first
     const long long H = lv.height[l];
     const double row_bytes = (double)lv.width[l] * (double)lv.channels * (double)es;
+    if (row_bytes * (double)H > up_bytes) {
+      sg->up_mask |= 1 << l;
+      continue;
+    }
     long long band = (long long)(budget / row_bytes);
     if (band < 1) band = 1;
     long long nb = (H + band - 1) / band;
@@ -709,9 +743,11 @@ bool make_segments(const LevelArgs& lv, size_t es, double budget, SegTable* sg) 
       sg->rows[i] = (int)((b + 1) * band <= H ? band : H - b * band);
     }
   }
-  for (int l = lv.num_levels; l < B200DET_MAX_LEVELS; ++l) {
-    sg->first_seg[l] = 0; sg->band_rows[l] = 1; sg->nbands[l] = 1;
-  }
+  if (sg->nseg == 0) return false;
+  for (int l = 0; l < B200DET_MAX_LEVELS; ++l)
+    if (l >= lv.num_levels || ((sg->up_mask >> l) & 1)) {
+      sg->first_seg[l] = sg->nseg - 1; sg->band_rows[l] = 0x7fffffff; sg->nbands[l] = 1;
+    }
   return true;
 }
 
@@ -761,7 +797,7 @@ int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool ve
   a.RP = a.mode == 1 ? kRowChunks : (PH + 1) / 2;
   a.vec = vec; a.aligned = aligned;
   a.plan = nullptr; a.order = nullptr; a.gsorted = nullptr; a.ngroups = 1; a.zero_chunk = 0; a.ztotal = 0; a.zlook = 1; a.zper = 1;
-  a.sg.nseg = 0;
+  a.sg.nseg = 0; a.sg.zup = 0; a.sg.up_mask = 0;
 
   DeviceScratch* s = scratch_for_current_device();
   const int sms = s && s->sms > 0 ? s->sms : 148;
@@ -780,7 +816,7 @@ int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool ve
     // streaming upstream gradient share it).
     const double budget = (double)env_int("B200DET_BWD_GROUP_MB", 20) * 1048576.0;
     bool seg = env_int("B200DET_BWD_PHASED", 0) != 0 && (double)image_bytes * (double)a.N > budget &&
-               make_segments(lv, sizeof(T), budget, &a.sg);
+               make_segments(lv, sizeof(T), budget, (double)env_int("B200DET_BWD_UP_MB", 32) * 1048576.0, &a.sg);
     if (seg && (long long)a.sg.nseg * a.N > kMaxGroups) seg = false;
     if (!seg) a.sg.nseg = 0;
     a.ngroups = seg ? a.sg.nseg * a.N : 1;
@@ -820,13 +856,22 @@ int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool ve
       a.zero_chunk = (int)zero_chunk;
       long long zt = 0;
       if (seg) {
+        a.sg.up_first[0] = 0;
+        for (int l = 0; l < B200DET_MAX_LEVELS; ++l) {
+          long long n = 0;
+          if (l < lv.num_levels && ((a.sg.up_mask >> l) & 1))
+            n = ((long long)a.N * lv.height[l] * lv.width[l] * C * (long long)sizeof(T) + zero_chunk - 1) / zero_chunk;
+          if (a.sg.up_first[l] + n >= 0x7fffffffLL) return 1;
+          a.sg.up_first[l + 1] = a.sg.up_first[l] + (int)n;
+        }
+        a.sg.zup = a.sg.up_first[B200DET_MAX_LEVELS];
         for (int i = 0; i < a.sg.nseg; ++i) {
           const long long bytes = (long long)a.sg.rows[i] * lv.width[a.sg.level[i]] * C * (long long)sizeof(T);
           a.sg.zfirst[i] = (int)zt;
           zt += (bytes + zero_chunk - 1) / zero_chunk;
         }
         a.sg.zfirst[a.sg.nseg] = (int)zt;
-        zt *= a.N;
+        zt = zt * a.N + a.sg.zup;
       } else {
         for (int l = 0; l < lv.num_levels; ++l) {
           const long long bytes = (long long)a.N * lv.height[l] * lv.width[l] * C * (long long)sizeof(T);
