@@ -26,6 +26,7 @@ SYMBOLS = [
     "b200det_nms_workspace_bytes", "b200det_nms", "b200det_batched_nms", "b200det_roi_align_forward_host",
     "b200det_roi_align_backward_host", "b200det_msroi_align_forward_host", "b200det_msroi_align_backward_host",
     "b200det_nms_host", "b200det_batched_nms_host", "b200det_host_release",
+    "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented",
 ]
 
 _declared = False
@@ -58,6 +59,9 @@ def lib():
         l.b200det_nms_host.argtypes = [_P, _P, _I, _L, _D, _P, _P, _I]
         l.b200det_batched_nms_host.argtypes = [_P, _P, _P, _I, _L, _D, _I, _P, _P, _I]
         l.b200det_host_release.restype = None
+        l.b200det_nms_segmented_workspace_bytes.argtypes = [_L, _P, _L]
+        l.b200det_nms_segmented_workspace_bytes.restype = _S
+        l.b200det_nms_segmented.argtypes = [_P, _P, _P, _P, _I, _L, _P, _L, _D, _I, _L, _P, _P, _P, _S, _P]
         _declared = True
     return l
 
@@ -234,6 +238,43 @@ def batched_nms(boxes, scores, idxs, iou_threshold, mode=BNMS_AUTO, workspace: O
     if not sync:
         return w.keep, cnt
     return w.keep[: int(cnt.item())].clone()
+
+
+def nms_segmented(boxes, scores, idxs, seg_offsets: Sequence[int], iou_threshold, valid=None, mode=BNMS_AUTO,
+                  top_n=0, sync=True):
+    """Per-image class-aware NMS over S box sets in one launch sequence (b200det_nms_segmented).
+
+    seg_offsets: S + 1 host integers.  Returns a list of S index tensors (sync=True; ONE read-back of
+    the S counts) or (keep, counts) still on the device: set s owns keep[off[s] : off[s] + counts[s]].
+    Indices are positions in the concatenated `boxes`."""
+    boxes = boxes.contiguous()
+    scores = scores.to(boxes.dtype).contiguous()
+    n = boxes.shape[0]
+    off = torch.as_tensor(list(seg_offsets), dtype=torch.int64)
+    S = off.numel() - 1
+    if idxs is not None:
+        idxs = idxs.to(torch.int64).contiguous()
+    if valid is not None:
+        valid = valid.to(torch.uint8).contiguous()
+    keep = torch.empty(max(n, 1), dtype=torch.int64, device=boxes.device)
+    counts = torch.zeros(max(S, 1), dtype=torch.int64, device=boxes.device)
+    if S > 0:
+        nbytes = lib().b200det_nms_segmented_workspace_bytes(n, off.data_ptr(), S)
+        if nbytes == 0:
+            raise B200DetError("nms_segmented: seg_offsets must be a non-decreasing partition of [0, N)")
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=boxes.device)
+        with torch.cuda.device(boxes.device):
+            _check(lib().b200det_nms_segmented(boxes.data_ptr(), scores.data_ptr(),
+                                               idxs.data_ptr() if idxs is not None else None,
+                                               valid.data_ptr() if valid is not None else None, _dt(boxes), n,
+                                               off.data_ptr(), S, float(iou_threshold), int(mode), int(top_n),
+                                               keep.data_ptr(), counts.data_ptr(), ws.data_ptr(), nbytes,
+                                               _stream(boxes)), "b200det_nms_segmented")
+    if not sync:
+        return keep, counts[:S]
+    c = counts[:S].tolist()
+    o = off.tolist()
+    return [keep[o[s]: o[s] + c[s]] for s in range(S)]
 
 
 # --------------------------------------------------------------------------- host-buffer entry points

@@ -248,4 +248,27 @@ int b200det_batched_nms(const void* boxes, const void* scores, const int64_t* id
                     workspace_bytes, (cudaStream_t)stream);
 }
 
+size_t b200det_nms_segmented_workspace_bytes(int64_t N, const int64_t* seg_offsets, int64_t S) {
+  if (N < 0 || S < 0 || !seg_offsets) return 0;
+  return nms_segmented_workspace_bytes(N, seg_offsets, S);
+}
+
+int b200det_nms_segmented(const void* boxes, const void* scores, const int64_t* idxs, const uint8_t* valid,
+                          int dtype, int64_t N, const int64_t* seg_offsets, int64_t S, double iou_threshold,
+                          int mode, int64_t top_n, int64_t* keep, int64_t* counts, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+  if (N < 0 || S < 0) return fail(B200DET_EINVAL, "nms_segmented: negative N or S");
+  if (S > 0 && !counts) return fail(B200DET_EINVAL, "nms_segmented: null counts");
+  if (N > 0 && (!boxes || !scores || !keep || !workspace)) return fail(B200DET_EINVAL, "nms_segmented: null pointer");
+  int m;
+  if (!idxs) m = 0;
+  else if (mode == B200DET_BNMS_AUTO) m = -1;
+  else if (mode == B200DET_BNMS_COORD_TRICK) m = 1;
+  else if (mode == B200DET_BNMS_VANILLA) m = 2;
+  else return fail(B200DET_EINVAL, "nms_segmented: unknown mode %d", mode);
+  const int tn = top_n > 0x7fffffffLL ? 0x7fffffff : (int)top_n;
+  return nms_segmented_device(boxes, scores, idxs, valid, dtype, N, seg_offsets, S, iou_threshold, m, tn, keep, counts,
+                              workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
 }  // extern "C"

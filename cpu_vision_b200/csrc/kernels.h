@@ -53,4 +53,10 @@ int nms_device(const void* boxes, const void* scores, const int64_t* idxs, int d
                double thr, int mode, int64_t* keep, int64_t* num_keep, void* ws, size_t ws_bytes,
                cudaStream_t st);
 
+// segmented (per-image) NMS; seg_offsets is a HOST array of S + 1 box offsets; mode -1 auto / 0 plain / 1 trick / 2 vanilla
+size_t nms_segmented_workspace_bytes(long long N, const int64_t* seg_offsets, long long S);
+int nms_segmented_device(const void* boxes, const void* scores, const int64_t* idxs, const uint8_t* valid,
+                         int dtype, long long N, const int64_t* seg_offsets, long long S, double thr, int mode,
+                         int top_n, int64_t* keep, int64_t* counts, void* ws, size_t ws_bytes, cudaStream_t st);
+
 }  // namespace b200det

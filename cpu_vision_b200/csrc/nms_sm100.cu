@@ -137,12 +137,9 @@ __global__ void nms_gather_kernel(const T* __restrict__ boxes, const int64_t* __
 // grid = (col_blocks, col_blocks); tiles below the diagonal exit at once and
 // their words are never read (the scan starts at the diagonal word).
 template <typename BoxT>
-__global__ void __launch_bounds__(kTile) nms_mask_kernel(int n, float thr,
-                                                         const BoxT* __restrict__ boxes,
-                                                         const int32_t* __restrict__ cls,
-                                                         u64* __restrict__ mask) {
-  const int row_start = blockIdx.y, col_start = blockIdx.x;
-  if (row_start > col_start) return;
+__device__ __forceinline__ void mask_tile(int n, float thr, const BoxT* __restrict__ boxes,
+                                          const int32_t* __restrict__ cls, u64* __restrict__ mask,
+                                          int row_start, int col_start) {
   const int row_size = min(n - row_start * kTile, kTile);
   const int col_size = min(n - col_start * kTile, kTile);
   __shared__ BoxT cb[kTile];
@@ -163,6 +160,31 @@ __global__ void __launch_bounds__(kTile) nms_mask_kernel(int n, float thr,
     const int col_blocks = (n + kTile - 1) / kTile;
     mask[(long long)cur * col_blocks + col_start] = t;
   }
+}
+
+template <typename BoxT>
+__global__ void __launch_bounds__(kTile) nms_mask_kernel(int n, float thr,
+                                                         const BoxT* __restrict__ boxes,
+                                                         const int32_t* __restrict__ cls,
+                                                         u64* __restrict__ mask) {
+  const int row_start = blockIdx.y, col_start = blockIdx.x;
+  if (row_start > col_start) return;
+  mask_tile<BoxT>(n, thr, boxes, cls, mask, row_start, col_start);
+}
+
+// segmented: blockIdx.z = segment (image); boxes of segment s are sorted[off[s] .. off[s+1])
+template <typename BoxT>
+__global__ void __launch_bounds__(kTile) nms_seg_mask_kernel(const int32_t* __restrict__ off,
+                                                             const long long* __restrict__ moff,
+                                                             const int32_t* __restrict__ smode, float thr,
+                                                             const BoxT* __restrict__ boxes,
+                                                             const int32_t* __restrict__ cls,
+                                                             u64* __restrict__ mask) {
+  const int s = blockIdx.z;
+  const int o = off[s], n = off[s + 1] - o;
+  const int row_start = blockIdx.y, col_start = blockIdx.x;
+  if (row_start > col_start || col_start * kTile >= n) return;
+  mask_tile<BoxT>(n, thr, boxes + o, smode[s] == 2 ? cls + o : nullptr, mask + moff[s], row_start, col_start);
 }
 
 // ---- 5. greedy scan -----------------------------------------------------------
@@ -195,7 +217,7 @@ __device__ __forceinline__ u64 resolve_block(u64 alive, const u64* __restrict__ 
 // compaction of the kept bits: running offset over words, blockDim.x words per pass
 __device__ __forceinline__ void compact_keep(const u64* keptw, int col_blocks, const int32_t* __restrict__ order,
                                              int64_t* __restrict__ keep, int64_t* __restrict__ num_keep,
-                                             int* s_base, u64* s_total) {
+                                             int* s_base, u64* s_total, int top_n = 0) {
   const int tid = threadIdx.x, nthreads = blockDim.x, nwarps = nthreads >> 5;
   int running = 0;
   for (int w0 = 0; w0 < col_blocks; w0 += nthreads) {
@@ -230,12 +252,12 @@ __device__ __forceinline__ void compact_keep(const u64* keptw, int col_blocks, c
     running += (int)*s_total;
     __syncthreads();
   }
-  if (tid == 0) *num_keep = running;
+  if (tid == 0) *num_keep = (top_n > 0 && running > top_n) ? top_n : running;
 }
 
-__global__ void __launch_bounds__(kSmemThreads) nms_scan_smem_kernel(
+__device__ __forceinline__ void scan_smem_body(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
-    int64_t* __restrict__ keep, int64_t* __restrict__ num_keep) {
+    int64_t* __restrict__ keep, int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n) {
   extern __shared__ u64 smem[];
   u64* remv = smem;                     // [col_blocks]
   u64* keptw = smem + col_blocks;       // [col_blocks]
@@ -243,7 +265,7 @@ __global__ void __launch_bounds__(kSmemThreads) nms_scan_smem_kernel(
   __shared__ u64 s_kept;
   __shared__ int s_base[32];
   const int tid = threadIdx.x;
-  for (int j = tid; j < col_blocks; j += kSmemThreads) remv[j] = 0;
+  for (int j = tid; j < col_blocks; j += kSmemThreads) remv[j] = init_remv ? init_remv[j] : 0ULL;
 
   auto prefetch = [&](int b) {  // words j >= b of the rows of block b; a warp copies whole rows
     u64* dst = stage + (size_t)(b & 1) * kTile * col_blocks;
@@ -299,12 +321,29 @@ __global__ void __launch_bounds__(kSmemThreads) nms_scan_smem_kernel(
     }
     __syncthreads();  // stage (b & 1) is refilled by the prefetch of block b + 2
   }
-  compact_keep(keptw, col_blocks, order, keep, num_keep, s_base, &s_kept);
+  compact_keep(keptw, col_blocks, order, keep, num_keep, s_base, &s_kept, top_n);
 }
 
-__global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
+__global__ void __launch_bounds__(kSmemThreads) nms_scan_smem_kernel(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
     int64_t* __restrict__ keep, int64_t* __restrict__ num_keep) {
+  scan_smem_body(mask, n, col_blocks, order, keep, num_keep, nullptr, 0);
+}
+
+// segmented: one CTA per segment, all segments scan concurrently
+__global__ void __launch_bounds__(kSmemThreads) nms_seg_scan_smem_kernel(
+    const u64* __restrict__ mask, const int32_t* __restrict__ off, const long long* __restrict__ moff,
+    const int32_t* __restrict__ roff, const int32_t* __restrict__ order, int64_t* __restrict__ keep,
+    int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n) {
+  const int s = blockIdx.x;
+  const int o = off[s], n = off[s + 1] - o;
+  scan_smem_body(mask + moff[s], n, (n + kTile - 1) / kTile, order + o, keep + o, num_keep + s,
+                 init_remv + roff[s], top_n);
+}
+
+__device__ __forceinline__ void scan_body(
+    const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
+    int64_t* __restrict__ keep, int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n) {
   extern __shared__ u64 smem[];
   u64* remv = smem;                 // [col_blocks]
   u64* keptw = smem + col_blocks;   // [col_blocks]
@@ -312,7 +351,7 @@ __global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
   __shared__ u64 s_kept;
   __shared__ int s_base[kScanThreads / 32];
   const int tid = threadIdx.x;
-  for (int j = tid; j < col_blocks; j += kScanThreads) remv[j] = 0;
+  for (int j = tid; j < col_blocks; j += kScanThreads) remv[j] = init_remv ? init_remv[j] : 0ULL;
   __syncthreads();
 
   for (int b = 0; b < col_blocks; ++b) {
@@ -340,7 +379,23 @@ __global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
     }
     __syncthreads();
   }
-  compact_keep(keptw, col_blocks, order, keep, num_keep, s_base, &s_kept);
+  compact_keep(keptw, col_blocks, order, keep, num_keep, s_base, &s_kept, top_n);
+}
+
+__global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
+    const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
+    int64_t* __restrict__ keep, int64_t* __restrict__ num_keep) {
+  scan_body(mask, n, col_blocks, order, keep, num_keep, nullptr, 0);
+}
+
+__global__ void __launch_bounds__(kScanThreads) nms_seg_scan_kernel(
+    const u64* __restrict__ mask, const int32_t* __restrict__ off, const long long* __restrict__ moff,
+    const int32_t* __restrict__ roff, const int32_t* __restrict__ order, int64_t* __restrict__ keep,
+    int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n) {
+  const int s = blockIdx.x;
+  const int o = off[s], n = off[s + 1] - o;
+  scan_body(mask + moff[s], n, (n + kTile - 1) / kTile, order + o, keep + o, num_keep + s, init_remv + roff[s],
+            top_n);
 }
 
 __global__ void nms_zero_count_kernel(int64_t* num_keep) { *num_keep = 0; }
@@ -436,6 +491,243 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
   return 0;
 }
 
+// ---- segmented NMS: S independent box sets (images) in one launch sequence -------------------
+// Replaces the per-image Python loops around batched_nms in RegionProposalNetwork.filter_proposals
+// (models/detection/rpn.py:268-297) and RoIHeads.postprocess_detections (roi_heads.py:693-723).
+constexpr int kSegBatch = 64;
+struct SegBatch {
+  int count, base;
+  int off[kSegBatch + 1];          // first box of segment base + j
+  long long moff[kSegBatch + 1];   // first mask word
+  int roff[kSegBatch + 1];         // first remv word
+  signed char mode[kSegBatch + 1]; // 0 plain, 1 coordinate trick, 2 vanilla (class compare)
+};
+
+__global__ void nms_seg_setup_kernel(const __grid_constant__ SegBatch b, int32_t* __restrict__ off,
+                                     long long* __restrict__ moff, int32_t* __restrict__ roff,
+                                     int32_t* __restrict__ smode) {
+  const int j = threadIdx.x;
+  if (j <= b.count) {
+    off[b.base + j] = b.off[j];
+    moff[b.base + j] = b.moff[j];
+    roff[b.base + j] = b.roff[j];
+    smode[b.base + j] = b.mode[j];
+  }
+}
+
+// segment of global position i: largest s with off[s] <= i
+__device__ __forceinline__ int seg_of(const int32_t* __restrict__ off, int S, int i) {
+  int lo = 0, hi = S;  // off[lo] <= i < off[hi]
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(off + mid) <= i) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// 64-bit sort key: segment in the high word, the score mapped so that an ASCENDING sort gives
+// descending scores in the low word; equal scores keep ascending index (stable radix sort), like
+// scores.sort(stable=True, descending=True).  Boxes filtered out before NMS go last.
+template <typename T>
+__global__ void nms_seg_keys_kernel(const T* __restrict__ scores, const uint8_t* __restrict__ valid, int n,
+                                    const int32_t* __restrict__ off, int S, u64* __restrict__ keys,
+                                    int32_t* __restrict__ idx) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float f = (float)Io<T>::ld(scores + i);
+  if (f == 0.f) f = 0.f;  // -0 sorts like +0
+  const unsigned bits = __float_as_uint(f);
+  const unsigned asc = bits ^ ((bits >> 31) ? 0xffffffffu : 0x80000000u);
+  unsigned low = ~asc;
+  if (valid && !valid[i]) low = 0xffffffffu;
+  keys[i] = ((u64)(unsigned)seg_of(off, S, i) << 32) | (u64)low;
+  idx[i] = i;
+}
+
+// boxes.max() of every segment's surviving boxes (coordinate trick, boxes.py:91); one CTA per segment
+template <typename T>
+__global__ void nms_seg_max_kernel(const T* __restrict__ boxes, const uint8_t* __restrict__ valid,
+                                   const int32_t* __restrict__ off, float* __restrict__ out) {
+  __shared__ float red[32];
+  const int s = blockIdx.x;
+  float m = -INFINITY;
+  bool nan = false;
+  for (int i = off[s] + threadIdx.x; i < off[s + 1]; i += blockDim.x) {
+    if (valid && !valid[i]) continue;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const float v = (float)Io<T>::ld(boxes + (long long)i * 4 + c);
+      nan |= (v != v);
+      m = v > m ? v : m;
+    }
+  }
+  if (nan) m = NAN;
+  for (int o = 16; o > 0; o >>= 1) {
+    const float other = __shfl_xor_sync(0xffffffffu, m, o);
+    m = (other != other || m != m) ? NAN : (other > m ? other : m);
+  }
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    m = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : -INFINITY;
+    for (int o = 16; o > 0; o >>= 1) {
+      const float other = __shfl_xor_sync(0xffffffffu, m, o);
+      m = (other != other || m != m) ? NAN : (other > m ? other : m);
+    }
+    if (threadIdx.x == 0) out[s] = m;
+  }
+}
+
+// boxes into (segment, score) order; mode as nms_gather_kernel; filtered boxes start out removed
+template <typename T>
+__global__ void nms_seg_gather_kernel(const T* __restrict__ boxes, const int64_t* __restrict__ idxs,
+                                      const uint8_t* __restrict__ valid, const int32_t* __restrict__ order, int n,
+                                      const int32_t* __restrict__ off, const int32_t* __restrict__ roff, int S,
+                                      const int32_t* __restrict__ smode, const float* __restrict__ max_coord,
+                                      Box4f* __restrict__ sorted, int32_t* __restrict__ sorted_cls,
+                                      u64* __restrict__ init_remv) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const long long src = order[i];
+  const int s = seg_of(off, S, i);
+  float x1 = (float)Io<T>::ld(boxes + src * 4 + 0), y1 = (float)Io<T>::ld(boxes + src * 4 + 1);
+  float x2 = (float)Io<T>::ld(boxes + src * 4 + 2), y2 = (float)Io<T>::ld(boxes + src * 4 + 3);
+  const int mode = smode[s];
+  if (mode == 1) {
+    const float o = __fmul_rn((float)idxs[src], __fadd_rn(max_coord[s], 1.f));
+    x1 = __fadd_rn(x1, o); y1 = __fadd_rn(y1, o);
+    x2 = __fadd_rn(x2, o); y2 = __fadd_rn(y2, o);
+  }
+  Box4f b;
+  b.x1 = x1; b.y1 = y1; b.x2 = x2; b.y2 = y2;
+  sorted[i] = b;
+  if (idxs) sorted_cls[i] = (int32_t)idxs[src];
+  if (valid && !valid[src]) {
+    const int p = i - off[s];
+    atomicOr(init_remv + roff[s] + (p >> 6), 1ULL << (p & 63));
+  }
+}
+
+struct SegLayout {
+  u64 *keys_in, *keys_out, *mask, *init_remv;
+  int32_t *idx_in, *order, *cls, *off, *roff, *smode;
+  long long* moff;
+  float* maxc;
+  Box4f* sorted;
+  void* cub_tmp;
+  size_t cub_bytes, total;
+};
+
+size_t cub_temp_bytes_u64(long long n) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const u64*)nullptr, (u64*)nullptr, (const int32_t*)nullptr,
+                                  (int32_t*)nullptr, (int)n);
+  return bytes;
+}
+
+SegLayout seg_carve(void* ws, long long n, long long S, long long mask_words, long long remv_words) {
+  SegLayout L;
+  Carve c{(char*)ws, 0, 0};
+  L.keys_in = (u64*)c.take(n * 8);
+  L.keys_out = (u64*)c.take(n * 8);
+  L.idx_in = (int32_t*)c.take(n * 4);
+  L.order = (int32_t*)c.take(n * 4);
+  L.cls = (int32_t*)c.take(n * 4);
+  L.off = (int32_t*)c.take((S + 1) * 4);
+  L.roff = (int32_t*)c.take((S + 1) * 4);
+  L.smode = (int32_t*)c.take((S + 1) * 4);
+  L.moff = (long long*)c.take((S + 1) * 8);
+  L.maxc = (float*)c.take((S + 1) * 4);
+  L.sorted = (Box4f*)c.take(n * sizeof(Box4f));
+  L.init_remv = (u64*)c.take((remv_words + 1) * 8);
+  L.cub_bytes = cub_temp_bytes_u64(n);
+  L.cub_tmp = c.take(L.cub_bytes);
+  L.mask = (u64*)c.take((size_t)(mask_words + 1) * 8);
+  L.total = c.off + 256;
+  return L;
+}
+
+// host-side shape of the segmentation: returns false when the offsets are not a partition of [0, N)
+bool seg_shape(const int64_t* seg_offsets, long long S, long long N, long long* mask_words, long long* remv_words,
+               int* cb_max) {
+  *mask_words = 0; *remv_words = 0; *cb_max = 0;
+  if (S < 0 || (S == 0 && N != 0)) return false;
+  if (S == 0) return true;
+  if (seg_offsets[0] != 0 || seg_offsets[S] != N) return false;
+  for (long long s = 0; s < S; ++s) {
+    const long long n = seg_offsets[s + 1] - seg_offsets[s];
+    if (n < 0) return false;
+    const long long cb = (n + kTile - 1) / kTile;
+    *mask_words += n * cb;
+    *remv_words += cb;
+    if (cb > *cb_max) *cb_max = (int)cb;
+  }
+  return true;
+}
+
+template <typename T>
+int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const uint8_t* valid, long long n,
+              const int64_t* seg_offsets, long long S, double thr, int mode, int top_n, int64_t* keep,
+              int64_t* counts, void* ws, cudaStream_t st) {
+  long long mask_words, remv_words;
+  int cb_max;
+  seg_shape(seg_offsets, S, n, &mask_words, &remv_words, &cb_max);
+  const SegLayout L = seg_carve(ws, n, S, mask_words, remv_words);
+  // segment tables: host offsets travel as kernel parameters, 64 segments per launch
+  long long mo = 0;
+  int ro = 0;
+  for (long long base = 0; base < S; base += kSegBatch) {
+    SegBatch b;
+    b.base = (int)base;
+    b.count = (int)((S - base) < kSegBatch ? (S - base) : kSegBatch);
+    for (int j = 0; j <= b.count; ++j) {
+      b.off[j] = (int)seg_offsets[base + j];
+      b.moff[j] = mo;
+      b.roff[j] = ro;
+      b.mode[j] = 0;
+      if (j < b.count) {
+        const long long ns = seg_offsets[base + j + 1] - seg_offsets[base + j];
+        // mode < 0: the reference's rule for a CUDA tensor, image by image (boxes.py:72)
+        b.mode[j] = (signed char)(!idxs ? 0 : (mode >= 0 ? mode : (4 * ns > 20000 ? 2 : 1)));
+        const long long cb = (ns + kTile - 1) / kTile;
+        mo += ns * cb;
+        ro += (int)cb;
+      }
+    }
+    nms_seg_setup_kernel<<<1, kSegBatch + 1, 0, st>>>(b, L.off, L.moff, L.roff, L.smode);
+  }
+  const int th = 256, bl = (int)((n + th - 1) / th);
+  nms_seg_keys_kernel<T><<<bl, th, 0, st>>>((const T*)scores, valid, (int)n, L.off, (int)S, L.keys_in, L.idx_in);
+  int seg_bits = 1;
+  while ((1LL << seg_bits) < S) ++seg_bits;
+  B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairs(L.cub_tmp, const_cast<size_t&>(L.cub_bytes), (const u64*)L.keys_in,
+                                                  L.keys_out, (const int32_t*)L.idx_in, L.order, (int)n, 0,
+                                                  32 + seg_bits, st));
+  if (idxs && mode != 2) nms_seg_max_kernel<T><<<(unsigned)S, 256, 0, st>>>((const T*)boxes, valid, L.off, L.maxc);
+  B200DET_CUDA_OK(cudaMemsetAsync(L.init_remv, 0, (size_t)(remv_words + 1) * 8, st));
+  nms_seg_gather_kernel<T><<<bl, th, 0, st>>>((const T*)boxes, idxs, valid, L.order, (int)n, L.off, L.roff, (int)S,
+                                              L.smode, L.maxc, L.sorted, L.cls, L.init_remv);
+  if (cb_max > 0) {
+    dim3 grid(cb_max, cb_max, (unsigned)S);
+    nms_seg_mask_kernel<Box4f><<<grid, kTile, 0, st>>>(L.off, L.moff, L.smode, (float)thr, L.sorted, L.cls, L.mask);
+  }
+  if (cb_max <= kSmemBlocks) {
+    const size_t smem = ((size_t)2 * cb_max + (size_t)2 * kTile * cb_max) * sizeof(u64) + 16;
+    if (smem > 48 * 1024)
+      B200DET_CUDA_OK(cudaFuncSetAttribute(nms_seg_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    nms_seg_scan_smem_kernel<<<(unsigned)S, kSmemThreads, smem, st>>>(L.mask, L.off, L.moff, L.roff, L.order, keep,
+                                                                      counts, L.init_remv, top_n);
+  } else {
+    const size_t smem = (size_t)cb_max * 16 + 16;
+    if (smem > 48 * 1024)
+      B200DET_CUDA_OK(cudaFuncSetAttribute(nms_seg_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    nms_seg_scan_kernel<<<(unsigned)S, kScanThreads, smem, st>>>(L.mask, L.off, L.moff, L.roff, L.order, keep, counts,
+                                                                 L.init_remv, top_n);
+  }
+  B200DET_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace
 
 size_t nms_workspace_bytes(long long N) {
@@ -463,6 +755,38 @@ int nms_device(const void* boxes, const void* scores, const int64_t* idxs, int d
     case B200DET_F64: return nms_t<double>(boxes, scores, idxs, N, thr, mode, keep, num_keep, ws, st);
   }
   return fail(B200DET_ENOSUP, "nms: unknown dtype %d", dtype);
+}
+
+size_t nms_segmented_workspace_bytes(long long N, const int64_t* seg_offsets, long long S) {
+  long long mw, rw;
+  int cbm;
+  if (!seg_shape(seg_offsets, S, N, &mw, &rw, &cbm)) return 0;
+  return seg_carve(nullptr, N > 0 ? N : 1, S, mw, rw).total;
+}
+
+int nms_segmented_device(const void* boxes, const void* scores, const int64_t* idxs, const uint8_t* valid, int dtype,
+                         long long N, const int64_t* seg_offsets, long long S, double thr, int mode, int top_n,
+                         int64_t* keep, int64_t* counts, void* ws, size_t ws_bytes, cudaStream_t st) {
+  long long mw, rw;
+  int cbm;
+  if (!seg_offsets || !seg_shape(seg_offsets, S, N, &mw, &rw, &cbm))
+    return fail(B200DET_EINVAL, "nms_segmented: seg_offsets must be a non-decreasing partition of [0, N)");
+  if (S == 0) return 0;
+  if (N >= 0x7fffffffLL || S > 65535) return fail(B200DET_EINVAL, "nms_segmented: N=%lld S=%lld too large", N, S);
+  if ((long long)cbm * 16 > 200 * 1024)
+    return fail(B200DET_ENOSUP, "nms_segmented: a segment exceeds the single-CTA scan capacity");
+  if (N == 0) {
+    B200DET_CUDA_OK(cudaMemsetAsync(counts, 0, (size_t)S * 8, st));
+    return 0;
+  }
+  const size_t need = nms_segmented_workspace_bytes(N, seg_offsets, S);
+  if (ws_bytes < need) return fail(B200DET_EWORKSPACE, "nms_segmented: workspace %zu < required %zu", ws_bytes, need);
+  switch (dtype) {
+    case B200DET_F32: return nms_seg_t<float>(boxes, scores, idxs, valid, N, seg_offsets, S, thr, mode, top_n, keep, counts, ws, st);
+    case B200DET_F16: return nms_seg_t<__half>(boxes, scores, idxs, valid, N, seg_offsets, S, thr, mode, top_n, keep, counts, ws, st);
+    case B200DET_BF16: return nms_seg_t<__nv_bfloat16>(boxes, scores, idxs, valid, N, seg_offsets, S, thr, mode, top_n, keep, counts, ws, st);
+  }
+  return fail(B200DET_ENOSUP, "nms_segmented: dtype %d not supported (fp32 / fp16 / bf16 boxes)", dtype);
 }
 
 }  // namespace b200det

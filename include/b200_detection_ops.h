@@ -185,6 +185,29 @@ int b200det_batched_nms(
     int64_t N, double iou_threshold, int mode, int64_t* keep,
     int64_t* num_keep, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Segmented (per-image) class-aware NMS: S independent box sets in ONE launch
+ * sequence, every set scanned by its own CTA.  Replaces the per-image Python
+ * loops around batched_nms in RegionProposalNetwork.filter_proposals
+ * (torchvision/models/detection/rpn.py:268-297) and
+ * RoIHeads.postprocess_detections (roi_heads.py:693-723); per segment the
+ * result is exactly batched_nms(boxes[valid], scores[valid], idxs[valid], thr)
+ * mapped back to original indices and cut to the first top_n entries.
+ *   seg_offsets : HOST int64 [S + 1], boxes of set s are [off[s], off[s+1])
+ *   idxs        : device int64 [N] categories, or NULL (plain nms per set)
+ *   valid       : device uint8 [N] or NULL; 0 = box was filtered out before
+ *                 NMS (small-box / score filters keep static shapes this way)
+ *   mode        : b200det_bnms_mode; AUTO applies the reference's rule
+ *                 (boxes.py:72) to every set on its own box count
+ *   top_n       : <= 0: no limit
+ *   keep        : device int64 [N]; set s owns keep[off[s] .. off[s] + counts[s])
+ *   counts      : device int64 [S] */
+size_t b200det_nms_segmented_workspace_bytes(int64_t N, const int64_t* seg_offsets, int64_t S);
+int b200det_nms_segmented(
+    const void* boxes, const void* scores, const int64_t* idxs,
+    const uint8_t* valid, int dtype, int64_t N, const int64_t* seg_offsets,
+    int64_t S, double iou_threshold, int mode, int64_t top_n, int64_t* keep,
+    int64_t* counts, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------
  * Host-buffer entry points (what a CPU-tensor caller of the reference binds).
  * Inputs and outputs are HOST pointers; the call stages them through a

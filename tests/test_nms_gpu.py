@@ -191,3 +191,79 @@ def test_full_size_properties(capi):
     assert ok.any(dim=1).all()
     again = capi.batched_nms(bd[keep], sd[keep], idd[keep], thr, capi.BNMS_VANILLA)
     assert torch.equal(again, torch.arange(keep.numel(), device=DEV))
+
+
+# ---- segmented (per-image) NMS: b200det_nms_segmented ------------------------------------------
+def _segmented_oracle(b, s, i, off, thr, valid, mode, top_n):
+    """Per image: batched_nms of the surviving boxes, mapped back to positions in the concatenation
+    (what the Python loops of rpn.py:268-297 / roi_heads.py:693-723 compute)."""
+    out = []
+    for k in range(len(off) - 1):
+        sel = torch.arange(off[k], off[k + 1])
+        if valid is not None:
+            sel = sel[valid[sel].bool()]
+        if sel.numel() == 0:
+            out.append(torch.empty(0, dtype=torch.int64))
+            continue
+        if i is None:
+            keep = oracle.nms(b[sel], s[sel], thr)
+        else:
+            m = mode if mode != "auto" else ("vanilla" if 4 * (off[k + 1] - off[k]) > 20000 else "trick")
+            keep = oracle.batched_nms(b[sel], s[sel], i[sel], thr, m)
+        keep = sel[keep]
+        out.append(keep[:top_n] if top_n > 0 else keep)
+    return out
+
+
+@pytest.mark.parametrize("sizes", [[5], [0, 7, 0], [64, 65, 1, 130], [700, 1, 0, 333, 1200], [300] * 70])
+@pytest.mark.parametrize("mode", ["plain", "trick", "vanilla"])
+def test_segmented_vs_oracle(capi, sizes, mode):
+    g = torch.Generator().manual_seed(sum(sizes) + len(mode))
+    n = sum(sizes)
+    off = [0]
+    for z in sizes:
+        off.append(off[-1] + z)
+    b, s = make_boxes(g, max(n, 1), span=200.0)
+    b, s = b[:n], s[:n]
+    i = None if mode == "plain" else torch.randint(0, 5, (n,), generator=g)
+    for valid, top_n in ((None, 0), (torch.rand(n, generator=g) > 0.3, 0), (None, 50)):
+        want = _segmented_oracle(b, s, i, off, 0.5, valid, mode, top_n)
+        got = capi.nms_segmented(b.to(DEV), s.to(DEV), None if i is None else i.to(DEV), off, 0.5,
+                                 valid=None if valid is None else valid.to(DEV),
+                                 mode={"plain": capi.BNMS_AUTO, "trick": capi.BNMS_TRICK, "vanilla": capi.BNMS_VANILLA}[mode],
+                                 top_n=top_n)
+        assert len(got) == len(want)
+        for k, (a, w) in enumerate(zip(got, want)):
+            assert torch.equal(a.cpu(), w), (sizes, mode, k, top_n)
+
+
+def test_segmented_auto_mode_and_negative_coordinates(capi):
+    """AUTO picks the strategy per image from its box count (boxes.py:72); with negative coordinates the
+    coordinate trick lets boxes of different classes meet, and that reference behaviour is kept."""
+    g = torch.Generator().manual_seed(77)
+    sizes = [5200, 900]  # vanilla for the first image, trick for the second
+    off = [0, 5200, 6100]
+    b, s = make_boxes(g, 6100, span=400.0)
+    b = b - 150.0
+    i = torch.randint(0, 4, (6100,), generator=g)
+    want = _segmented_oracle(b, s, i, off, 0.5, None, "auto", 0)
+    got = capi.nms_segmented(b.to(DEV), s.to(DEV), i.to(DEV), off, 0.5)
+    for a, w in zip(got, want):
+        assert torch.equal(a.cpu(), w)
+
+
+def test_segmented_equals_loop_of_batched_nms_full_size(capi):
+    """64 images x 4663 RPN candidates (5 levels): one segmented call == 64 batched_nms calls."""
+    g = torch.Generator().manual_seed(5)
+    per, S = 4663, 64
+    b, s = make_boxes(g, per * S, span=1000.0)
+    s = torch.cat([torch.randperm(per, generator=g).float() / per for _ in range(S)])  # distinct per image
+    lvl = torch.randint(0, 5, (per * S,), generator=g)
+    off = [k * per for k in range(S + 1)]
+    bd, sd, ld = b.to(DEV), s.to(DEV), lvl.to(DEV)
+    got = capi.nms_segmented(bd, sd, ld, off, 0.7, top_n=1000)
+    for k in (0, 17, 63):
+        sl = slice(off[k], off[k + 1])
+        ref = capi.batched_nms(bd[sl], sd[sl], ld[sl], 0.7)[:1000] + off[k]
+        assert torch.equal(got[k], ref)
+        assert torch.equal(got[k].cpu(), _segmented_oracle(b, s, lvl, off, 0.7, None, "auto", 1000)[k]) if k == 0 else True
