@@ -437,6 +437,42 @@ def secondary_legs(capi, dev, peak):
         "frac_of_bandwidth_bound": ((n * 20 + kept * 8) / (peak * 1e9)) / (ms / 1e3)}
     ms = timed(lambda: capi.nms(boxes, scores, 0.5, workspace=ws, sync=False), flush_l2=False)
     res["nms_5000"] = {"ms": ms, "boxes_per_s": n / (ms / 1e3)}
+    # cfg5 (RPN side): filter_proposals for 64 images of 800x1088, 5 FPN levels x 3 anchors,
+    # rpn_pre_nms_top_n = rpn_post_nms_top_n = 2000 (8663 candidates per image): the batched path
+    # (clip/filter kernel + ONE segmented NMS) next to the reference's shape of the same work -- a Python
+    # loop of per-image batched_nms calls -- both on our kernels, both ending with the boxes on the device
+    from cpu_vision_b200 import detection
+
+    B = 64
+    napl = [200 * 272 * 3, 100 * 136 * 3, 50 * 68 * 3, 25 * 34 * 3, 13 * 17 * 3]
+    A = sum(napl)
+    ctr = torch.rand(B, A, 2, generator=gen, device=dev) * torch.tensor([1088.0, 800.0], device=dev)
+    wh = torch.exp(torch.rand(B, A, 2, generator=gen, device=dev) * 3.5 + 2.5)
+    props = torch.cat([ctr - wh / 2, ctr + wh / 2], 2)
+    obj = torch.randn(B * A, 1, generator=gen, device=dev)
+    shapes = [(800, 1088)] * B
+    f1_ms = timed(lambda: detection.filter_proposals(props, obj, shapes, napl, 2000, 2000, 0.7), iters=5,
+                  flush_l2=False)
+    o2 = obj.reshape(B, -1)
+    idx = detection._get_top_n_idx(o2, napl, 2000)
+    bi = torch.arange(B, device=dev)[:, None]
+    pb, ps = props[bi, idx], torch.sigmoid(o2[bi, idx])
+    lv = torch.cat([torch.full((n_,), i_, dtype=torch.int64, device=dev) for i_, n_ in enumerate(napl)])[idx]
+    per = pb.shape[1]
+    off = [i * per for i in range(B + 1)]
+    pbf, psf, lvf = pb.reshape(-1, 4).contiguous(), ps.reshape(-1).contiguous(), lv.reshape(-1).contiguous()
+    seg_ms = timed(lambda: capi.nms_segmented(pbf, psf, lvf, off, 0.7, top_n=2000, sync=False), iters=10,
+                   flush_l2=False)
+
+    def loop():
+        return [capi.batched_nms(pb[i], ps[i], lv[i], 0.7)[:2000] for i in range(B)]
+
+    loop_ms = timed(loop, iters=3, flush_l2=False)
+    res["cfg5_rpn_postprocess_64img"] = {
+        "candidates_per_image": per, "filter_proposals_ms": f1_ms,
+        "filter_proposals_boxes_per_s": B * per / (f1_ms / 1e3),
+        "nms_segmented_ms": seg_ms, "nms_segmented_boxes_per_s": B * per / (seg_ms / 1e3),
+        "per_image_loop_of_batched_nms_ms": loop_ms, "speedup_vs_loop": loop_ms / seg_ms}
     return res
 
 

@@ -26,7 +26,7 @@ SYMBOLS = [
     "b200det_nms_workspace_bytes", "b200det_nms", "b200det_batched_nms", "b200det_roi_align_forward_host",
     "b200det_roi_align_backward_host", "b200det_msroi_align_forward_host", "b200det_msroi_align_backward_host",
     "b200det_nms_host", "b200det_batched_nms_host", "b200det_host_release",
-    "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented",
+    "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented", "b200det_clip_filter_boxes",
 ]
 
 _declared = False
@@ -62,6 +62,7 @@ def lib():
         l.b200det_nms_segmented_workspace_bytes.argtypes = [_L, _P, _L]
         l.b200det_nms_segmented_workspace_bytes.restype = _S
         l.b200det_nms_segmented.argtypes = [_P, _P, _P, _P, _I, _L, _P, _L, _D, _I, _L, _P, _P, _P, _S, _P]
+        l.b200det_clip_filter_boxes.argtypes = [_P, _P, _I, _L, _P, _L, _P, _D, _D, _I, _P, _P, _P]
         _declared = True
     return l
 
@@ -275,6 +276,23 @@ def nms_segmented(boxes, scores, idxs, seg_offsets: Sequence[int], iou_threshold
     c = counts[:S].tolist()
     o = off.tolist()
     return [keep[o[s]: o[s] + c[s]] for s in range(S)]
+
+
+def clip_filter_boxes(boxes, scores, seg_offsets: Sequence[int], image_shapes, min_size, score_thresh, strict):
+    """Clipped boxes + validity byte per box (b200det_clip_filter_boxes); image_shapes: S (height, width)."""
+    boxes = boxes.contiguous()
+    scores = scores.to(boxes.dtype).contiguous()
+    n = boxes.shape[0]
+    off = torch.tensor(list(seg_offsets), dtype=torch.int32, device=boxes.device)
+    sizes = torch.tensor([[float(h), float(w)] for h, w in image_shapes], dtype=torch.float32, device=boxes.device)
+    out = torch.empty_like(boxes)
+    valid = torch.empty(max(n, 1), dtype=torch.uint8, device=boxes.device)
+    with torch.cuda.device(boxes.device):
+        _check(lib().b200det_clip_filter_boxes(boxes.data_ptr(), scores.data_ptr(), _dt(boxes), n, off.data_ptr(),
+                                               off.numel() - 1, sizes.data_ptr(), float(min_size), float(score_thresh),
+                                               int(bool(strict)), out.data_ptr(), valid.data_ptr(), _stream(boxes)),
+               "b200det_clip_filter_boxes")
+    return out, valid[:n]
 
 
 # --------------------------------------------------------------------------- host-buffer entry points

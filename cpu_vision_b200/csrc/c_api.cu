@@ -271,4 +271,17 @@ int b200det_nms_segmented(const void* boxes, const void* scores, const int64_t* 
                               workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+int b200det_clip_filter_boxes(const void* boxes, const void* scores, int dtype, int64_t N,
+                              const int32_t* seg_offsets_dev, int64_t S, const float* image_sizes_dev,
+                              double min_size, double score_thresh, int strict, void* boxes_out, uint8_t* valid,
+                              void* stream) {
+  if (N < 0 || S < 0) return fail(B200DET_EINVAL, "clip_filter_boxes: negative N or S");
+  if (N == 0) return 0;
+  if (S == 0 || S > 0x7fffffffLL) return fail(B200DET_EINVAL, "clip_filter_boxes: N > 0 needs 1 <= S < 2^31 segments");
+  if (!boxes || !scores || !seg_offsets_dev || !image_sizes_dev || !boxes_out || !valid)
+    return fail(B200DET_EINVAL, "clip_filter_boxes: null pointer");
+  return clip_filter_boxes(boxes, scores, dtype, N, seg_offsets_dev, (int)S, image_sizes_dev, min_size, score_thresh,
+                           strict, boxes_out, valid, (cudaStream_t)stream);
+}
+
 }  // extern "C"

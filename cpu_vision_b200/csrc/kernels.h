@@ -59,4 +59,9 @@ int nms_segmented_device(const void* boxes, const void* scores, const int64_t* i
                          int dtype, long long N, const int64_t* seg_offsets, long long S, double thr, int mode,
                          int top_n, int64_t* keep, int64_t* counts, void* ws, size_t ws_bytes, cudaStream_t st);
 
+// box_ops_sm100.cu: clip to the image + small-box and score filters as a validity byte (static shapes)
+int clip_filter_boxes(const void* boxes, const void* scores, int dtype, long long n, const int32_t* off, int S,
+                      const float* sizes, double min_size, double score_thresh, int strict, void* out,
+                      uint8_t* valid, cudaStream_t st);
+
 }  // namespace b200det

@@ -208,6 +208,19 @@ int b200det_nms_segmented(
     int64_t S, double iou_threshold, int mode, int64_t top_n, int64_t* keep,
     int64_t* counts, void* workspace, size_t workspace_bytes, void* stream);
 
+/* clip_boxes_to_image + remove_small_boxes + score threshold for all images in
+ * one pass, shapes kept static (torchvision/ops/boxes.py:115-174 as used by
+ * rpn.py:276-285 and roi_heads.py:693-714).
+ *   seg_offsets_dev : DEVICE int32 [S + 1]; image_sizes_dev: DEVICE float [S, 2] (height, width)
+ *   strict          : 0: score >= score_thresh (RPN), 1: score > score_thresh (RoIHeads)
+ *   boxes_out       : device [N, 4] clipped boxes (may alias boxes)
+ *   valid           : device uint8 [N], the `valid` input of b200det_nms_segmented */
+int b200det_clip_filter_boxes(
+    const void* boxes, const void* scores, int dtype, int64_t N,
+    const int32_t* seg_offsets_dev, int64_t S, const float* image_sizes_dev,
+    double min_size, double score_thresh, int strict, void* boxes_out,
+    uint8_t* valid, void* stream);
+
 /* ------------------------------------------------------------------------
  * Host-buffer entry points (what a CPU-tensor caller of the reference binds).
  * Inputs and outputs are HOST pointers; the call stages them through a
