@@ -136,29 +136,55 @@ __global__ void nms_gather_kernel(const T* __restrict__ boxes, const int64_t* __
 // ---- 4. IoU bit tiles ---------------------------------------------------------
 // grid = (col_blocks, col_blocks); tiles below the diagonal exit at once and
 // their words are never read (the scan starts at the diagonal word).
+// One CTA = one 64-box row block x kColTiles consecutive column blocks (a CTA per single tile is
+// launch-bound: 1.2 M CTAs of ~1 us for 64 images x 8663 boxes).  With a non-negative threshold a
+// pair that does not intersect cannot pass (inter = 0 -> IoU is 0 or NaN), so it skips the division.
+constexpr int kColTiles = 8;
+
 template <typename BoxT>
-__device__ __forceinline__ void mask_tile(int n, float thr, const BoxT* __restrict__ boxes,
-                                          const int32_t* __restrict__ cls, u64* __restrict__ mask,
-                                          int row_start, int col_start) {
+__device__ __forceinline__ bool boxes_meet(const BoxT& a, const BoxT& b) {
+  return fminf((float)a.x2, (float)b.x2) > fmaxf((float)a.x1, (float)b.x1) &&
+         fminf((float)a.y2, (float)b.y2) > fmaxf((float)a.y1, (float)b.y1);
+}
+template <>
+__device__ __forceinline__ bool boxes_meet<Box4d>(const Box4d& a, const Box4d& b) {
+  return fmin(a.x2, b.x2) > fmax(a.x1, b.x1) && fmin(a.y2, b.y2) > fmax(a.y1, b.y1);
+}
+
+template <typename BoxT>
+__device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restrict__ boxes,
+                                           const int32_t* __restrict__ cls, u64* __restrict__ mask,
+                                           int row_start, int col_group) {
+  const int col_blocks = (n + kTile - 1) / kTile;
   const int row_size = min(n - row_start * kTile, kTile);
-  const int col_size = min(n - col_start * kTile, kTile);
   __shared__ BoxT cb[kTile];
   __shared__ int32_t cc[kTile];
-  if ((int)threadIdx.x < col_size) {
-    cb[threadIdx.x] = boxes[kTile * col_start + threadIdx.x];
-    cc[threadIdx.x] = cls ? cls[kTile * col_start + threadIdx.x] : 0;
-  }
-  __syncthreads();
-  if ((int)threadIdx.x < row_size) {
-    const int cur = kTile * row_start + threadIdx.x;
-    const BoxT a = boxes[cur];
-    const int32_t ac = cls ? cls[cur] : 0;
-    u64 t = 0;
-    const int start = (row_start == col_start) ? threadIdx.x + 1 : 0;
-    for (int i = start; i < col_size; ++i)
-      if (cc[i] == ac && iou_gt(a, cb[i], thr)) t |= 1ULL << i;
-    const int col_blocks = (n + kTile - 1) / kTile;
-    mask[(long long)cur * col_blocks + col_start] = t;
+  const int cur = kTile * row_start + threadIdx.x;
+  const bool have_row = (int)threadIdx.x < row_size;
+  BoxT a = boxes[have_row ? cur : kTile * row_start];
+  const int32_t ac = (cls && have_row) ? cls[cur] : 0;
+  const bool skip_apart = thr >= 0.f;
+  for (int t = 0; t < kColTiles; ++t) {
+    const int col_start = col_group * kColTiles + t;
+    if (col_start >= col_blocks) break;
+    if (col_start < row_start) continue;
+    const int col_size = min(n - col_start * kTile, kTile);
+    __syncthreads();  // the previous tile's columns are no longer read
+    if ((int)threadIdx.x < col_size) {
+      cb[threadIdx.x] = boxes[kTile * col_start + threadIdx.x];
+      cc[threadIdx.x] = cls ? cls[kTile * col_start + threadIdx.x] : 0;
+    }
+    __syncthreads();
+    if (have_row) {
+      u64 w = 0;
+      const int start = (row_start == col_start) ? threadIdx.x + 1 : 0;
+      for (int i = start; i < col_size; ++i) {
+        if (cc[i] != ac) continue;
+        if (skip_apart && !boxes_meet(a, cb[i])) continue;
+        if (iou_gt(a, cb[i], thr)) w |= 1ULL << i;
+      }
+      mask[(long long)cur * col_blocks + col_start] = w;
+    }
   }
 }
 
@@ -167,9 +193,9 @@ __global__ void __launch_bounds__(kTile) nms_mask_kernel(int n, float thr,
                                                          const BoxT* __restrict__ boxes,
                                                          const int32_t* __restrict__ cls,
                                                          u64* __restrict__ mask) {
-  const int row_start = blockIdx.y, col_start = blockIdx.x;
-  if (row_start > col_start) return;
-  mask_tile<BoxT>(n, thr, boxes, cls, mask, row_start, col_start);
+  const int row_start = blockIdx.y, col_group = blockIdx.x;
+  if (row_start > col_group * kColTiles + kColTiles - 1) return;
+  mask_tiles<BoxT>(n, thr, boxes, cls, mask, row_start, col_group);
 }
 
 // segmented: blockIdx.z = segment (image); boxes of segment s are sorted[off[s] .. off[s+1])
@@ -182,9 +208,10 @@ __global__ void __launch_bounds__(kTile) nms_seg_mask_kernel(const int32_t* __re
                                                              u64* __restrict__ mask) {
   const int s = blockIdx.z;
   const int o = off[s], n = off[s + 1] - o;
-  const int row_start = blockIdx.y, col_start = blockIdx.x;
-  if (row_start > col_start || col_start * kTile >= n) return;
-  mask_tile<BoxT>(n, thr, boxes + o, smode[s] == 2 ? cls + o : nullptr, mask + moff[s], row_start, col_start);
+  const int row_start = blockIdx.y, col_group = blockIdx.x;
+  if (row_start * kTile >= n || col_group * kColTiles * kTile >= n) return;
+  if (row_start > col_group * kColTiles + kColTiles - 1) return;
+  mask_tiles<BoxT>(n, thr, boxes + o, smode[s] == 2 ? cls + o : nullptr, mask + moff[s], row_start, col_group);
 }
 
 // ---- 5. greedy scan -----------------------------------------------------------
@@ -196,13 +223,13 @@ __global__ void __launch_bounds__(kTile) nms_seg_mask_kernel(const int32_t* __re
 // word; (b) all threads OR the kept rows into the words to the right.  Finally the
 // kept bits are compacted into keep[].
 //
-// nms_scan_smem_kernel (col_blocks <= kSmemBlocks, i.e. N <= 6144 -- the detection
+// nms_scan_smem_kernel (col_blocks <= kSmemBlocks, i.e. N <= 13312 -- the detection
 // sizes): the 64 mask rows of block b+1 are prefetched into shared memory with
 // cp.async while block b is resolved, so no step waits on L2.
 // nms_scan_kernel (any N): rows of kept boxes are read from global memory.
 constexpr int kScanThreads = 1024;
 constexpr int kSmemThreads = 512;
-constexpr int kSmemBlocks = 96;
+constexpr int kSmemBlocks = 208;  // 1040 bytes of shared memory per block: 211 KB
 
 __device__ __forceinline__ u64 resolve_block(u64 alive, const u64* __restrict__ diag, int stride) {
   u64 d[kTile];
@@ -473,7 +500,7 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
     nms_max_coord_kernel<T><<<1, 1024, 0, st>>>((const T*)boxes, n * 4, (A*)L.maxc);
   nms_gather_kernel<T><<<bl, th, 0, st>>>((const T*)boxes, idxs, L.order, n, mode, (const A*)L.maxc,
                                           (BoxT*)L.sorted, mode == 2 ? L.cls : nullptr);
-  dim3 grid(col_blocks, col_blocks);
+  dim3 grid((col_blocks + kColTiles - 1) / kColTiles, col_blocks);
   nms_mask_kernel<BoxT><<<grid, kTile, 0, st>>>((int)n, (float)thr, (const BoxT*)L.sorted,
                                                mode == 2 ? L.cls : nullptr, L.mask);
   if (col_blocks <= kSmemBlocks) {
@@ -708,7 +735,7 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
   nms_seg_gather_kernel<T><<<bl, th, 0, st>>>((const T*)boxes, idxs, valid, L.order, (int)n, L.off, L.roff, (int)S,
                                               L.smode, L.maxc, L.sorted, L.cls, L.init_remv);
   if (cb_max > 0) {
-    dim3 grid(cb_max, cb_max, (unsigned)S);
+    dim3 grid((cb_max + kColTiles - 1) / kColTiles, cb_max, (unsigned)S);
     nms_seg_mask_kernel<Box4f><<<grid, kTile, 0, st>>>(L.off, L.moff, L.smode, (float)thr, L.sorted, L.cls, L.mask);
   }
   if (cb_max <= kSmemBlocks) {
