@@ -468,6 +468,25 @@ def secondary_legs(capi, dev, peak):
         return [capi.batched_nms(pb[i], ps[i], lv[i], 0.7)[:2000] for i in range(B)]
 
     loop_ms = timed(loop, iters=3, flush_l2=False)
+    del props, obj, ctr, wh, pb, ps, lv, pbf, psf, lvf
+    # cfg3 as an NCHW caller sees it (the reference's models hand NCHW-contiguous features to roi_align):
+    # the dispatcher shim re-lays out -> channels_last kernels -> re-lays out; results are NCHW-contiguous
+    import cpu_vision_b200  # noqa: F401
+
+    feats, rois, grad = make_cfg3(dev, torch.float32, 1237)
+    fn, gn = [f.contiguous() for f in feats], grad.contiguous()
+    del feats, grad
+    lvl = capi.fpn_level_map(rois, 2, 5)
+    hs_, ws_ = [h for h, _ in SHAPES], [w for _, w in SHAPES]
+    nf = timed(lambda: torch.ops.b200det.msroi_align(fn, rois, SCALES, 14, 14, 2, False, 2, 5, 224, 4, 1e-6), iters=5,
+               flush_l2=False)
+    nb = timed(lambda: torch.ops.b200det.msroi_align_backward(gn, rois, lvl, SCALES, hs_, ws_, 16, C, 14, 14, 2, False,
+                                                              False), iters=5, flush_l2=False)
+    res["cfg3_fp32_nchw_caller"] = {
+        "fwd_ms": nf, "bwd_ms": nb, "fwd_bwd_rois_per_s": rois.shape[0] / ((nf + nb) / 1e3),
+        "path": "b200det_relayout NCHW->NHWC, channels_last kernels, b200det_relayout back (inside the timed region)",
+        "generic_strided_kernels_ms": "fwd 9.3 / bwd 11.4 (tools/kbench_nchw.py, B200DET_NCHW_RELAYOUT=0)"}
+    del fn, gn
     res["cfg5_rpn_postprocess_64img"] = {
         "candidates_per_image": per, "filter_proposals_ms": f1_ms,
         "filter_proposals_boxes_per_s": B * per / (f1_ms / 1e3),

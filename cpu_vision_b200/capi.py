@@ -26,7 +26,7 @@ SYMBOLS = [
     "b200det_nms_workspace_bytes", "b200det_nms", "b200det_batched_nms", "b200det_roi_align_forward_host",
     "b200det_roi_align_backward_host", "b200det_msroi_align_forward_host", "b200det_msroi_align_backward_host",
     "b200det_nms_host", "b200det_batched_nms_host", "b200det_host_release",
-    "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented", "b200det_clip_filter_boxes",
+    "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented", "b200det_clip_filter_boxes", "b200det_relayout",
 ]
 
 _declared = False
@@ -63,6 +63,7 @@ def lib():
         l.b200det_nms_segmented_workspace_bytes.restype = _S
         l.b200det_nms_segmented.argtypes = [_P, _P, _P, _P, _I, _L, _P, _L, _D, _I, _L, _P, _P, _P, _S, _P]
         l.b200det_clip_filter_boxes.argtypes = [_P, _P, _I, _L, _P, _L, _P, _D, _D, _I, _P, _P, _P]
+        l.b200det_relayout.argtypes = [_P, _P, _I, _L, _L, _L, _P]
         _declared = True
     return l
 
@@ -293,6 +294,23 @@ def clip_filter_boxes(boxes, scores, seg_offsets: Sequence[int], image_shapes, m
                                                int(bool(strict)), out.data_ptr(), valid.data_ptr(), _stream(boxes)),
                "b200det_clip_filter_boxes")
     return out, valid[:n]
+
+
+def relayout(t, to_channels_last: bool):
+    """[N,C,H,W] tensor, dense in one memory format -> the same values dense in the other (b200det_relayout)."""
+    N, Cc, H, W = t.shape
+    if to_channels_last:
+        src = t.contiguous()
+        dst = torch.empty_like(src, memory_format=torch.channels_last)
+        rows, cols = Cc, H * W
+    else:
+        src = t.contiguous(memory_format=torch.channels_last)
+        dst = torch.empty(t.shape, dtype=t.dtype, device=t.device)
+        rows, cols = H * W, Cc
+    with torch.cuda.device(t.device):
+        _check(lib().b200det_relayout(src.data_ptr(), dst.data_ptr(), _dt(t), N, rows, cols, _stream(t)),
+               "b200det_relayout")
+    return dst
 
 
 # --------------------------------------------------------------------------- host-buffer entry points

@@ -284,4 +284,12 @@ int b200det_clip_filter_boxes(const void* boxes, const void* scores, int dtype, 
                            strict, boxes_out, valid, (cudaStream_t)stream);
 }
 
+int b200det_relayout(const void* src, void* dst, int dtype, int64_t batch, int64_t rows, int64_t cols,
+                     void* stream) {
+  if (batch < 0 || rows < 0 || cols < 0) return fail(B200DET_EINVAL, "relayout: negative size");
+  if (batch * rows * cols == 0) return 0;
+  if (!src || !dst || src == dst) return fail(B200DET_EINVAL, "relayout: null or aliasing pointers");
+  return relayout(src, dst, dtype, batch, rows, cols, (cudaStream_t)stream);
+}
+
 }  // extern "C"

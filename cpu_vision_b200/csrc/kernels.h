@@ -64,4 +64,7 @@ int clip_filter_boxes(const void* boxes, const void* scores, int dtype, long lon
                       const float* sizes, double min_size, double score_thresh, int strict, void* out,
                       uint8_t* valid, cudaStream_t st);
 
+// relayout_sm100.cu: dst[b][c][r] = src[b][r][c] (NCHW -> NHWC: R = C, S = H*W; back: R = H*W, S = C)
+int relayout(const void* src, void* dst, int dtype, long long B, long long R, long long S, cudaStream_t st);
+
 }  // namespace b200det

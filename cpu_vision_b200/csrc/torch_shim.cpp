@@ -64,6 +64,41 @@ void check_roi_dtype(const at::Tensor& feat, const at::Tensor& rois, const char*
 
 void* cur_stream() { return (void*)at::cuda::getCurrentCUDAStream().stream(); }
 
+// ---- NCHW callers --------------------------------------------------------------------------
+// The reference's kernels take NCHW (input.contiguous(), cuda/roi_align_kernel.cu:384) and that is
+// what its detection models hand over.  The generic strided kernels serve it at the reference's
+// parallelisation; the channels_last kernels are ~10x faster (cfg3: 9.4 -> 0.6 ms forward, 11.5 -> 1.0 ms
+// backward), and a re-layout pass runs at HBM rate.  So when the shapes qualify for the fast kernels
+// and the RoIs are not a handful, an NCHW caller is served by relayout -> fast kernel -> relayout,
+// and still gets NCHW-contiguous results.  B200DET_NCHW_RELAYOUT=0 keeps the generic kernels.
+bool fast_shape(int dt, int64_t C, int64_t PH, int64_t PW, int64_t sr) {
+  return dt != B200DET_F64 && C > 0 && C % 128 == 0 && (sr == 1 || sr == 2) && PW >= 1 && PW * sr <= 32 &&
+         PH >= 1 && PH <= 32;
+}
+bool relayout_pays(int64_t K, int64_t PH, int64_t PW, int64_t feature_pixels) {
+  static const bool on = [] {
+    const char* e = getenv("B200DET_NCHW_RELAYOUT");
+    return !e || atoi(e) != 0;
+  }();
+  // a generic output element costs about as much as 16 feature elements of re-layout
+  return on && K > 0 && K * PH * PW * 16 >= feature_pixels;
+}
+// dense NCHW -> the same values with channels_last strides
+at::Tensor to_nhwc(const at::Tensor& t, int dt, const char* who) {
+  const at::Tensor src = t.contiguous();
+  at::Tensor dst = at::empty(src.sizes(), src.options().memory_format(at::MemoryFormat::ChannelsLast));
+  check_rc(b200det_relayout(src.data_ptr(), dst.data_ptr(), dt, src.size(0), src.size(1), src.size(2) * src.size(3),
+                            cur_stream()), who);
+  return dst;
+}
+// channels_last-dense -> NCHW-contiguous
+at::Tensor to_nchw(const at::Tensor& t, int dt, const char* who) {
+  at::Tensor dst = at::empty(t.sizes(), t.options().memory_format(at::MemoryFormat::Contiguous));
+  check_rc(b200det_relayout(t.data_ptr(), dst.data_ptr(), dt, t.size(0), t.size(2) * t.size(3), t.size(1),
+                            cur_stream()), who);
+  return dst;
+}
+
 // ---- torchvision::roi_align ------------------------------------------------
 at::Tensor roi_align_forward_cuda(const at::Tensor& input, const at::Tensor& rois,
                                   double spatial_scale, int64_t pooled_height,
@@ -79,10 +114,13 @@ at::Tensor roi_align_forward_cuda(const at::Tensor& input, const at::Tensor& roi
   at::cuda::CUDAGuard device_guard(input.device());
 
   const int dt = dtype_code(input.scalar_type(), "roi_align_forward_kernel");
-  const bool nhwc = is_nhwc(input);
-  const at::Tensor input_ = nhwc ? input : input.contiguous();
-  const at::Tensor rois_ = arith_rois(rois, input.scalar_type());
   const auto K = rois.size(0), C = input.size(1), H = input.size(2), W = input.size(3);
+  const bool via_nhwc = !is_nhwc(input) && fast_shape(dt, C, pooled_height, pooled_width, sampling_ratio) &&
+                        relayout_pays(K, pooled_height, pooled_width, input.size(0) * H * W);
+  const bool nhwc = via_nhwc || is_nhwc(input);
+  const at::Tensor input_ = via_nhwc ? to_nhwc(input, dt, "roi_align_forward_kernel")
+                                     : (nhwc ? input : input.contiguous());
+  const at::Tensor rois_ = arith_rois(rois, input.scalar_type());
   at::Tensor output = at::empty(
       {K, C, pooled_height, pooled_width},
       input.options().memory_format(nhwc ? at::MemoryFormat::ChannelsLast : at::MemoryFormat::Contiguous));
@@ -93,7 +131,7 @@ at::Tensor roi_align_forward_cuda(const at::Tensor& input, const at::Tensor& roi
                                      pooled_width, spatial_scale, (int)sampling_ratio, aligned,
                                      cur_stream()),
            "roi_align_forward_kernel");
-  return output;
+  return via_nhwc ? to_nchw(output, dt, "roi_align_forward_kernel") : output;
 }
 
 at::Tensor roi_align_backward_cuda(const at::Tensor& grad, const at::Tensor& rois,
@@ -113,15 +151,20 @@ at::Tensor roi_align_backward_cuda(const at::Tensor& grad, const at::Tensor& roi
   // grad_input follows the memory format the gradient arrives in: a
   // channels_last forward produced a channels_last output, whose gradient
   // normally comes back channels_last as well.
-  const bool nhwc = is_nhwc(grad);
+  const bool via_nhwc = !is_nhwc(grad) && grad.dim() == 4 && grad.numel() > 0 &&
+                        fast_shape(dt, channels, pooled_height, pooled_width, sampling_ratio) &&
+                        relayout_pays(rois.size(0), pooled_height, pooled_width, batch_size * height * width);
+  const bool nhwc = via_nhwc || is_nhwc(grad);
   at::Tensor grad_input = at::empty(
       {batch_size, channels, height, width},
       grad.options().memory_format(nhwc ? at::MemoryFormat::ChannelsLast : at::MemoryFormat::Contiguous));
   if (grad.numel() == 0) return grad_input.zero_();
   const at::Tensor rois_ = arith_rois(rois, grad.scalar_type());
-  const int64_t gs[4] = {grad.stride(0), grad.stride(1), grad.stride(2), grad.stride(3)};
+  const at::Tensor grad_ = via_nhwc ? to_nhwc(grad, dt, "roi_align_backward_kernel") : grad;
+  const int64_t gs[4] = {grad_.stride(0), grad_.stride(1), grad_.stride(2), grad_.stride(3)};
+  auto done = [&]() { return via_nhwc ? to_nchw(grad_input, dt, "roi_align_backward_kernel") : grad_input; };
   auto run = [&](int flags) {
-    return b200det_roi_align_backward(grad.data_ptr(), gs, rois_.data_ptr(), grad_input.data_ptr(),
+    return b200det_roi_align_backward(grad_.data_ptr(), gs, rois_.data_ptr(), grad_input.data_ptr(),
                                       nhwc ? B200DET_NHWC : B200DET_NCHW, dt, batch_size, channels, height,
                                       width, rois.size(0), pooled_height, pooled_width, spatial_scale,
                                       (int)sampling_ratio, aligned, flags, cur_stream());
@@ -130,12 +173,12 @@ at::Tensor roi_align_backward_cuda(const at::Tensor& grad, const at::Tensor& roi
   // reproducible; only where it does not apply does the reference's alert fire (:440)
   if (at::globalContext().deterministicAlgorithms()) {
     const int rc = run(B200DET_BWD_ZERO_INIT | B200DET_BWD_DETERMINISTIC);
-    if (rc == 0) return grad_input;
+    if (rc == 0) return done();
     TORCH_CHECK(rc == B200DET_ENOSUP, "roi_align_backward_kernel failed (", rc, "): ", b200det_last_error());
   }
   at::globalContext().alertNotDeterministic("roi_align_backward_kernel");
   check_rc(run(B200DET_BWD_ZERO_INIT), "roi_align_backward_kernel");
-  return grad_input;
+  return done();
 }
 
 // ---- torchvision::nms ---------------------------------------------------------
@@ -205,7 +248,11 @@ std::tuple<at::Tensor, at::Tensor> msroi_align_forward_cuda(
   check_roi_dtype(f0, rois, "msroi_align");
   at::cuda::CUDAGuard device_guard(f0.device());
   const int dt = dtype_code(f0.scalar_type(), "msroi_align");
-  const bool nhwc = is_nhwc(f0);
+  int64_t pixels = 0;
+  for (int l = 0; l < L; ++l) pixels += feats[l].dim() == 4 ? f0.size(0) * feats[l].size(2) * feats[l].size(3) : 0;
+  const bool via_nhwc = !is_nhwc(f0) && fast_shape(dt, f0.size(1), pooled_height, pooled_width, sampling_ratio) &&
+                        relayout_pays(rois.size(0), pooled_height, pooled_width, pixels);
+  const bool nhwc = via_nhwc || is_nhwc(f0);
   std::vector<at::Tensor> hold(L);
   const void* ptrs[B200DET_MAX_LEVELS];
   int64_t hs[B200DET_MAX_LEVELS], ws[B200DET_MAX_LEVELS];
@@ -215,7 +262,8 @@ std::tuple<at::Tensor, at::Tensor> msroi_align_forward_cuda(
     TORCH_CHECK(f.is_cuda() && f.dim() == 4 && f.scalar_type() == f0.scalar_type() &&
                     f.size(0) == f0.size(0) && f.size(1) == f0.size(1) && f.device() == f0.device(),
                 "msroi_align: feature maps must agree in dtype, device, batch and channels");
-    hold[l] = nhwc ? f.contiguous(at::MemoryFormat::ChannelsLast) : f.contiguous();
+    hold[l] = via_nhwc ? to_nhwc(f, dt, "msroi_align_forward")
+                       : (nhwc ? f.contiguous(at::MemoryFormat::ChannelsLast) : f.contiguous());
     ptrs[l] = hold[l].data_ptr();
     hs[l] = f.size(2);
     ws[l] = f.size(3);
@@ -235,6 +283,7 @@ std::tuple<at::Tensor, at::Tensor> msroi_align_forward_cuda(
                                        (int)sampling_ratio, aligned, (int)k_min, (int)k_max,
                                        (int)canonical_scale, (int)canonical_level, eps, cur_stream()),
            "msroi_align_forward");
+  if (via_nhwc) output = to_nchw(output, dt, "msroi_align_forward");
   return {output, levels};
 }
 
@@ -254,6 +303,14 @@ std::vector<at::Tensor> msroi_align_backward_cuda(
   void* ptrs[B200DET_MAX_LEVELS];
   int64_t hs[B200DET_MAX_LEVELS], ws[B200DET_MAX_LEVELS];
   double sc[B200DET_MAX_LEVELS];
+  int64_t pixels = 0;
+  for (int l = 0; l < L; ++l) pixels += batch_size * heights[l] * widths[l];
+  const bool want_nhwc = channels_last;
+  const bool via_nhwc = !want_nhwc && grad.dim() == 4 && grad.numel() > 0 && !is_nhwc(grad) &&
+                        fast_shape(dt, channels, pooled_height, pooled_width, sampling_ratio) &&
+                        relayout_pays(rois.size(0), pooled_height, pooled_width, pixels);
+  channels_last = want_nhwc || via_nhwc;
+  const at::Tensor grad_ = via_nhwc ? to_nhwc(grad, dt, "msroi_align_backward") : grad;
   for (int l = 0; l < L; ++l) {
     out[l] = at::empty({batch_size, channels, heights[l], widths[l]},
                        grad.options().memory_format(channels_last ? at::MemoryFormat::ChannelsLast
@@ -265,21 +322,26 @@ std::vector<at::Tensor> msroi_align_backward_cuda(
   }
   const at::Tensor rois_ = arith_rois(rois, grad.scalar_type());
   const at::Tensor levels_ = levels.to(at::kInt).contiguous();
-  const int64_t gs[4] = {grad.stride(0), grad.stride(1), grad.stride(2), grad.stride(3)};
+  const int64_t gs[4] = {grad_.stride(0), grad_.stride(1), grad_.stride(2), grad_.stride(3)};
+  auto done = [&]() {
+    if (via_nhwc)
+      for (int l = 0; l < L; ++l) out[l] = to_nchw(out[l], dt, "msroi_align_backward");
+    return out;
+  };
   auto run = [&](int flags) {
-    return b200det_msroi_align_backward(grad.data_ptr(), gs, rois_.data_ptr(), levels_.data_ptr<int32_t>(), ptrs,
+    return b200det_msroi_align_backward(grad_.data_ptr(), gs, rois_.data_ptr(), levels_.data_ptr<int32_t>(), ptrs,
                                         hs, ws, sc, L, channels_last ? B200DET_NHWC : B200DET_NCHW, dt,
                                         batch_size, channels, rois.size(0), pooled_height, pooled_width,
                                         (int)sampling_ratio, aligned, flags, cur_stream());
   };
   if (at::globalContext().deterministicAlgorithms()) {
     const int rc = run(B200DET_BWD_ZERO_INIT | B200DET_BWD_DETERMINISTIC);
-    if (rc == 0) return out;
+    if (rc == 0) return done();
     TORCH_CHECK(rc == B200DET_ENOSUP, "msroi_align_backward failed (", rc, "): ", b200det_last_error());
   }
   at::globalContext().alertNotDeterministic("msroi_align_backward");
   check_rc(run(B200DET_BWD_ZERO_INIT), "msroi_align_backward");
-  return out;
+  return done();
 }
 
 at::Tensor fpn_level_map_cuda(const at::Tensor& rois, int64_t k_min, int64_t k_max,

@@ -221,6 +221,16 @@ int b200det_clip_filter_boxes(
     double min_size, double score_thresh, int strict, void* boxes_out,
     uint8_t* valid, void* stream);
 
+/* Batched transposition dst[b][c][r] = src[b][r][c] of `batch` dense
+ * [rows, cols] matrices: the NCHW <-> NHWC re-layout the dispatcher shim puts
+ * around the channels_last kernels for callers that hold NCHW-contiguous
+ * tensors, which is what the reference's kernels take
+ * (input.contiguous(), cuda/roi_align_kernel.cu:384).
+ *   NCHW -> NHWC: batch = N, rows = C, cols = H*W;  NHWC -> NCHW: rows = H*W, cols = C */
+int b200det_relayout(
+    const void* src, void* dst, int dtype, int64_t batch, int64_t rows,
+    int64_t cols, void* stream);
+
 /* ------------------------------------------------------------------------
  * Host-buffer entry points (what a CPU-tensor caller of the reference binds).
  * Inputs and outputs are HOST pointers; the call stages them through a

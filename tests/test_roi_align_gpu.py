@@ -443,8 +443,12 @@ def test_deterministic_mode_through_the_dispatcher():
         b = torch.ops.torchvision._roi_align_backward(god, rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False)
         assert torch.equal(a, b)
         close_bwd(a, want64)
-        with pytest.raises(RuntimeError):
-            torch.ops.torchvision._roi_align_backward(go.to(DEV), rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False)
+        # an NCHW gradient that qualifies for the fast kernels is re-laid out and takes the tile kernel too
+        c = torch.ops.torchvision._roi_align_backward(go.to(DEV), rois.to(DEV), sc, PH, PH, N, C, H, W, 2, False)
+        assert c.is_contiguous() and torch.equal(c, a.contiguous())
+        with pytest.raises(RuntimeError):  # C = 3: generic atomics kernel, alert like the reference
+            torch.ops.torchvision._roi_align_backward(go[:, :3].contiguous().to(DEV), rois.to(DEV), sc, PH, PH, N, 3,
+                                                      H, W, 2, False)
     finally:
         torch.use_deterministic_algorithms(False)
 
@@ -477,3 +481,72 @@ def test_msroi_align_host_entry_points_pipelined(golden, capi, channels_last):
     for a, b in zip(gis_p, d["grad_in_7"]):
         close_bwd(a, b, rtol=2e-5)
     capi.host_release()
+
+
+# ---- NCHW callers (the reference's default layout): relayout -> channels_last kernels -> relayout ---------
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16, torch.float64])
+@pytest.mark.parametrize("shape", [(1, 1, 1, 1), (2, 3, 5, 7), (3, 256, 40, 56), (2, 130, 33, 65), (1, 64, 1, 200)])
+def test_relayout_both_ways(capi, dtype, shape):
+    g = torch.Generator().manual_seed(sum(shape))
+    x = torch.randn(shape, generator=g).to(dtype).to(DEV)
+    cl = capi.relayout(x, True)
+    assert cl.is_contiguous(memory_format=torch.channels_last) and torch.equal(cl, x)
+    back = capi.relayout(cl, False)
+    assert back.is_contiguous() and torch.equal(back, x)
+
+
+def test_nchw_caller_takes_the_fast_kernels_through_the_dispatcher():
+    """Same tensors, NCHW-contiguous like the reference's models produce them: results are NCHW-contiguous,
+    equal to the channels_last call (same kernels) and to the oracle; autograd included."""
+    import cpu_vision_b200  # noqa: F401
+
+    g = torch.Generator().manual_seed(21)
+    N, C, H, W, K, PH = 2, 256, 50, 68, 300, 7
+    x = torch.randn(N, C, H, W, generator=g)
+    rois = rand_rois(g, K, N, W * 16.0, H * 16.0, lo=16.0)
+    want = oracle.roi_align_forward(x, rois, PH, PH, 0.0625, 2, True)
+    xd = x.to(DEV).requires_grad_(True)
+    y = torch.ops.torchvision.roi_align(xd, rois.to(DEV), 0.0625, PH, PH, 2, True)
+    assert y.is_contiguous()
+    close_fwd(y.detach(), want)
+    ycl = torch.ops.torchvision.roi_align(x.to(DEV).contiguous(memory_format=torch.channels_last), rois.to(DEV), 0.0625,
+                                          PH, PH, 2, True)
+    assert torch.equal(y.detach(), ycl.contiguous())
+    go = torch.randn(K, C, PH, PH, generator=g)
+    y.backward(go.to(DEV))
+    assert xd.grad.is_contiguous()
+    close_bwd(xd.grad, oracle.roi_align_backward(go.double(), rois.double(), 0.0625, PH, PH, N, C, H, W, 2, True))
+    # a handful of RoIs on a big map: the re-layout would cost more than it saves, generic kernel, same answer
+    few = rois[:2].to(DEV)
+    close_fwd(torch.ops.torchvision.roi_align(x.to(DEV), few, 0.0625, PH, PH, 2, True),
+              oracle.roi_align_forward(x, rois[:2], PH, PH, 0.0625, 2, True))
+
+
+def test_nchw_msroi_module_through_relayout(golden):
+    """MultiScaleRoIAlign mirror on NCHW features with C = 256: b200det::msroi_align re-lays out every level."""
+    from cpu_vision_b200.poolers import MultiScaleRoIAlign
+    from collections import OrderedDict
+
+    g = torch.Generator().manual_seed(5)
+    img = (256, 320)
+    feats = OrderedDict((str(i), torch.randn(2, 256, img[0] // (4 << i), img[1] // (4 << i), generator=g))
+                        for i in range(4))
+    boxes = []
+    for _ in range(2):
+        r = rand_rois(g, 150, 1, float(img[1]), float(img[0]), lo=8.0, hi=400.0)[:, 1:]
+        boxes.append(r)
+    m = MultiScaleRoIAlign(["0", "1", "2", "3"], 7, 2)
+    fd = OrderedDict((k, v.to(DEV).requires_grad_(True)) for k, v in feats.items())
+    y = m(fd, [b.to(DEV) for b in boxes], [img, img])
+    assert y.is_contiguous()
+    rois = torch.cat([torch.cat([torch.full((b.shape[0], 1), float(i)), b], 1) for i, b in enumerate(boxes)])
+    levels = oracle.fpn_level_map(rois, 2, 5)
+    scales = [1.0 / (4 << i) for i in range(4)]
+    want = oracle.msroi_align_forward(list(feats.values()), rois, levels, scales, 7, 7, 2, False)
+    close_fwd(y.detach(), want)
+    go = torch.randn(y.shape, generator=g)
+    y.backward(go.to(DEV))
+    wants = oracle.msroi_align_backward(go, rois, levels, scales, [tuple(f.shape) for f in feats.values()], 7, 7, 2, False)
+    for f, w_ in zip(fd.values(), wants):
+        assert f.grad.is_contiguous()
+        close_bwd(f.grad, w_)
