@@ -63,6 +63,8 @@ def source(rep, top=16):
         seen.add(name)
         rows = list(csv.reader(b[1:]))
         hdr = rows[0]
+        if "# Samples" not in hdr or "Instructions Executed" not in hdr:
+            continue  # kernels too short to be sampled
         iS, iE, iN = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("# Samples")
         stall_cols = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
         ops, samp, stalls, data = collections.Counter(), collections.Counter(), collections.Counter(), []
