@@ -27,6 +27,7 @@ SYMBOLS = [
     "b200det_roi_align_backward_host", "b200det_msroi_align_forward_host", "b200det_msroi_align_backward_host",
     "b200det_nms_host", "b200det_batched_nms_host", "b200det_host_release",
     "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented", "b200det_clip_filter_boxes", "b200det_relayout",
+    "b200det_roi_pool_forward", "b200det_roi_pool_backward",
 ]
 
 _declared = False
@@ -64,6 +65,8 @@ def lib():
         l.b200det_nms_segmented.argtypes = [_P, _P, _P, _P, _I, _L, _P, _L, _D, _I, _L, _P, _P, _P, _S, _P]
         l.b200det_clip_filter_boxes.argtypes = [_P, _P, _I, _L, _P, _L, _P, _D, _D, _I, _P, _P, _P]
         l.b200det_relayout.argtypes = [_P, _P, _I, _L, _L, _L, _P]
+        l.b200det_roi_pool_forward.argtypes = [_P, _I, _P, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _P]
+        l.b200det_roi_pool_backward.argtypes = [_P, _P, _P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _P]
         _declared = True
     return l
 
@@ -311,6 +314,33 @@ def relayout(t, to_channels_last: bool):
         _check(lib().b200det_relayout(src.data_ptr(), dst.data_ptr(), _dt(t), N, rows, cols, _stream(t)),
                "b200det_relayout")
     return dst
+
+
+def roi_pool_forward(x, rois, pooled_h, pooled_w, spatial_scale=1.0):
+    """(output, argmax int32) in x's memory format (b200det_roi_pool_forward)."""
+    layout, x = _layout_of(x)
+    r = _arith(rois, x.dtype)
+    N, Cc, H, W = x.shape
+    K = r.shape[0]
+    out = _empty_like_layout((K, Cc, pooled_h, pooled_w), x, layout)
+    am = torch.empty_like(out, dtype=torch.int32)  # same memory format as the output
+    with torch.cuda.device(x.device):
+        _check(lib().b200det_roi_pool_forward(x.data_ptr(), layout, r.data_ptr(), out.data_ptr(), am.data_ptr(), layout,
+                                              _dt(x), N, Cc, H, W, K, pooled_h, pooled_w, float(spatial_scale),
+                                              _stream(x)), "b200det_roi_pool_forward")
+    return out, am
+
+
+def roi_pool_backward(grad, rois, argmax, pooled_h, pooled_w, N, Cc, H, W, layout=NCHW):
+    """grad_input [N,C,H,W] in `layout`; argmax as returned by roi_pool_forward (its own layout is detected)."""
+    r = _arith(rois, grad.dtype)
+    am_layout, am = _layout_of(argmax)
+    gi = _empty_like_layout((N, Cc, H, W), grad, layout)
+    with torch.cuda.device(grad.device):
+        _check(lib().b200det_roi_pool_backward(grad.data_ptr(), _strides(grad), am.data_ptr(), am_layout, r.data_ptr(),
+                                               gi.data_ptr(), layout, _dt(grad), N, Cc, H, W, r.shape[0], pooled_h,
+                                               pooled_w, _stream(grad)), "b200det_roi_pool_backward")
+    return gi
 
 
 # --------------------------------------------------------------------------- host-buffer entry points

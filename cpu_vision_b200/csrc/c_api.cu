@@ -292,4 +292,32 @@ int b200det_relayout(const void* src, void* dst, int dtype, int64_t batch, int64
   return relayout(src, dst, dtype, batch, rows, cols, (cudaStream_t)stream);
 }
 
+int b200det_roi_pool_forward(const void* input, int in_layout, const void* rois, void* output, int32_t* argmax,
+                             int out_layout, int dtype, int64_t N, int64_t C, int64_t H, int64_t W, int64_t K,
+                             int64_t PH, int64_t PW, double spatial_scale, void* stream) {
+  int rc = check_common("roi_pool_forward", dtype, in_layout, out_layout, N, C, K, PH, PW);
+  if (rc) return rc;
+  if (H < 0 || W < 0 || H > INT32_MAX || W > INT32_MAX) return fail(B200DET_EINVAL, "roi_pool_forward: bad H or W");
+  if (K * C * PH * PW == 0) return 0;
+  if (!rois || !output || !argmax || (!input && N * C * H * W != 0))
+    return fail(B200DET_EINVAL, "roi_pool_forward: null pointer");
+  return roi_pool_forward(input, in_layout, rois, output, argmax, out_layout, dtype, N, C, H, W, K, (int)PH, (int)PW,
+                          spatial_scale, (cudaStream_t)stream);
+}
+
+int b200det_roi_pool_backward(const void* grad, const int64_t* grad_strides, const int32_t* argmax, int argmax_layout,
+                              const void* rois, void* grad_input, int gi_layout, int dtype, int64_t N, int64_t C,
+                              int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW, void* stream) {
+  int rc = check_common("roi_pool_backward", dtype, argmax_layout, gi_layout, N, C, K, PH, PW);
+  if (rc) return rc;
+  if (H < 0 || W < 0 || H > INT32_MAX || W > INT32_MAX) return fail(B200DET_EINVAL, "roi_pool_backward: bad H or W");
+  if (N * C * H * W == 0) return 0;
+  if (!grad_input) return fail(B200DET_EINVAL, "roi_pool_backward: null grad_input");
+  if (K * C * PH * PW != 0 && (!grad || !grad_strides || !argmax || !rois))
+    return fail(B200DET_EINVAL, "roi_pool_backward: null pointer");
+  static const int64_t zero4[4] = {0, 0, 0, 0};
+  return roi_pool_backward(grad, grad_strides ? grad_strides : zero4, argmax, argmax_layout, rois, grad_input, gi_layout,
+                           dtype, N, C, H, W, K, (int)PH, (int)PW, (cudaStream_t)stream);
+}
+
 }  // extern "C"

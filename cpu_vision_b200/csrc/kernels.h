@@ -67,4 +67,13 @@ int clip_filter_boxes(const void* boxes, const void* scores, int dtype, long lon
 // relayout_sm100.cu: dst[b][c][r] = src[b][r][c] (NCHW -> NHWC: R = C, S = H*W; back: R = H*W, S = C)
 int relayout(const void* src, void* dst, int dtype, long long B, long long R, long long S, cudaStream_t st);
 
+// roi_pool_sm100.cu: torchvision::roi_pool; argmax = h * W + w inside the channel plane (-1: empty bin), stored in the
+// output's layout; the backward zero-fills grad_in itself
+int roi_pool_forward(const void* input, int in_layout, const void* rois, void* out, int32_t* argmax, int out_layout,
+                     int dtype, long long N, long long C, long long H, long long W, long long K, int PH, int PW,
+                     double scale, cudaStream_t st);
+int roi_pool_backward(const void* grad, const int64_t* gs, const int32_t* argmax, int am_layout, const void* rois,
+                      void* grad_in, int gi_layout, int dtype, long long N, long long C, long long H, long long W,
+                      long long K, int PH, int PW, cudaStream_t st);
+
 }  // namespace b200det

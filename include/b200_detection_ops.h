@@ -231,6 +231,27 @@ int b200det_relayout(
     const void* src, void* dst, int dtype, int64_t batch, int64_t rows,
     int64_t cols, void* stream);
 
+/* torchvision::roi_pool (max pooling over integer bins).  Replaces
+ * roi_pool_forward_kernel / roi_pool_backward_kernel
+ * (torchvision/csrc/ops/cuda/roi_pool_kernel.cu:120-278; CPU twin
+ * cpu/roi_pool_kernel.cpp:127-249).  Same geometry as the reference: round()
+ * of the scaled corners, floor / ceil bin edges, empty bins give 0.
+ *   argmax : device int32 [K, C, PH, PW] in the output's layout; h * W + w
+ *            inside the channel plane, -1 for an empty bin (reference meaning)
+ *   rois   : as for roi_align (arithmetic type of the features)
+ * The backward zero-fills grad_input and honours arbitrary element strides of
+ * `grad` (roi_pool_kernel.cu:255-258). */
+int b200det_roi_pool_forward(
+    const void* input, int in_layout, const void* rois, void* output,
+    int32_t* argmax, int out_layout, int dtype, int64_t N, int64_t C,
+    int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+    double spatial_scale, void* stream);
+int b200det_roi_pool_backward(
+    const void* grad, const int64_t* grad_strides, const int32_t* argmax,
+    int argmax_layout, const void* rois, void* grad_input, int gi_layout,
+    int dtype, int64_t N, int64_t C, int64_t H, int64_t W, int64_t K,
+    int64_t PH, int64_t PW, void* stream);
+
 /* ------------------------------------------------------------------------
  * Host-buffer entry points (what a CPU-tensor caller of the reference binds).
  * Inputs and outputs are HOST pointers; the call stages them through a

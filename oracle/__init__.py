@@ -64,6 +64,12 @@ def _declare(l, impl):
         f = getattr(l, f"{pre}_nms_{sfx}")
         f.argtypes = [_P, _P, _L, _D, _I, _P] if impl == "oracle" else [_P, _P, _L, _D, _P]
         f.restype = _L
+        f = getattr(l, f"{pre}_roi_pool_forward_{sfx}")
+        f.argtypes = [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _D]
+        f.restype = None
+        f = getattr(l, f"{pre}_roi_pool_backward_{sfx}")
+        f.argtypes = [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, long_t, long_t, long_t, long_t]
+        f.restype = None
     if impl == "oracle":
         for name in ("oracle_batched_nms_trick_f32", "oracle_batched_nms_vanilla_f32"):
             f = getattr(l, name)
@@ -214,3 +220,33 @@ def msroi_align_backward(grad, rois, levels, scales, shapes, pooled_h, pooled_w,
                                           shapes[0][1], pooled_h, pooled_w, int(sampling_ratio),
                                           int(bool(aligned)))
     return outs
+
+
+def roi_pool_forward(x, rois, pooled_h, pooled_w, spatial_scale=1.0, impl="oracle"):
+    """cpu/roi_pool_kernel.cpp:127-186 -> (output, argmax int32), NCHW."""
+    x = _cpu(x).contiguous()
+    rois = _cpu(rois).to(x.dtype).contiguous()
+    N, Cc, H, W = x.shape
+    K = rois.shape[0]
+    out = torch.zeros(K, Cc, pooled_h, pooled_w, dtype=x.dtype)
+    am = torch.zeros(K, Cc, pooled_h, pooled_w, dtype=torch.int32)
+    pre = "oracle" if impl == "oracle" else "tvref"
+    if out.numel():
+        getattr(lib(impl), f"{pre}_roi_pool_forward_{_sfx(x)}")(x.data_ptr(), rois.data_ptr(), out.data_ptr(),
+                                                                am.data_ptr(), K, Cc, H, W, pooled_h, pooled_w,
+                                                                float(spatial_scale))
+    return out, am
+
+
+def roi_pool_backward(grad, rois, argmax, pooled_h, pooled_w, N, Cc, H, W, impl="oracle"):
+    """cpu/roi_pool_kernel.cpp:188-249 (grad strides honoured)."""
+    grad = _cpu(grad)
+    rois = _cpu(rois).to(grad.dtype).contiguous()
+    am = _cpu(argmax).to(torch.int32).contiguous()
+    gi = torch.zeros(N, Cc, H, W, dtype=grad.dtype)
+    pre = "oracle" if impl == "oracle" else "tvref"
+    if grad.numel():
+        getattr(lib(impl), f"{pre}_roi_pool_backward_{_sfx(grad)}")(grad.data_ptr(), am.data_ptr(), rois.data_ptr(),
+                                                                    gi.data_ptr(), rois.shape[0], Cc, H, W, pooled_h,
+                                                                    pooled_w, *grad.stride())
+    return gi

@@ -378,3 +378,75 @@ API void oracle_msroi_align_backward_f32(const float* grad, long gs_n, long gs_c
                                   pooled_width, scales[l], sampling_ratio, aligned);
   }
 }
+
+/* ---- roi_pool ---------------------------------------------------
+ * ops/../csrc/ops/cpu/roi_pool_kernel.cpp:16-83 (forward) and :85-125 (backward), NCHW,
+ * same loops, same float -> int conversions. */
+#include <float.h>
+
+#define ORACLE_ROI_POOL(T, SFX)                                                                       \
+  API void oracle_roi_pool_forward_##SFX(const T* input, const T* rois, T* output, int* argmax,      \
+                                         int num_rois, int channels, int height, int width, int ph_n, \
+                                         int pw_n, double scale_d) {                                  \
+    const T spatial_scale = (T)scale_d;                                                               \
+    for (int n = 0; n < num_rois; ++n) {                                                              \
+      const T* r = rois + n * 5;                                                                      \
+      int roi_batch_ind = (int)r[0];                                                                  \
+      int roi_start_w = (int)round(r[1] * spatial_scale);                                             \
+      int roi_start_h = (int)round(r[2] * spatial_scale);                                             \
+      int roi_end_w = (int)round(r[3] * spatial_scale);                                               \
+      int roi_end_h = (int)round(r[4] * spatial_scale);                                               \
+      int roi_width = roi_end_w - roi_start_w + 1;                                                    \
+      int roi_height = roi_end_h - roi_start_h + 1;                                                   \
+      if (roi_width < 1) roi_width = 1;                                                               \
+      if (roi_height < 1) roi_height = 1;                                                             \
+      T bin_size_h = (T)roi_height / (T)ph_n;                                                         \
+      T bin_size_w = (T)roi_width / (T)pw_n;                                                          \
+      for (int ph = 0; ph < ph_n; ++ph)                                                               \
+        for (int pw = 0; pw < pw_n; ++pw) {                                                           \
+          int hstart = (int)floor((T)ph * bin_size_h);                                                \
+          int wstart = (int)floor((T)pw * bin_size_w);                                                \
+          int hend = (int)ceil((T)(ph + 1) * bin_size_h);                                             \
+          int wend = (int)ceil((T)(pw + 1) * bin_size_w);                                             \
+          hstart = hstart + roi_start_h; hstart = hstart < 0 ? 0 : (hstart > height ? height : hstart); \
+          hend = hend + roi_start_h; hend = hend < 0 ? 0 : (hend > height ? height : hend);           \
+          wstart = wstart + roi_start_w; wstart = wstart < 0 ? 0 : (wstart > width ? width : wstart); \
+          wend = wend + roi_start_w; wend = wend < 0 ? 0 : (wend > width ? width : wend);             \
+          int is_empty = (hend <= hstart) || (wend <= wstart);                                        \
+          for (int c = 0; c < channels; ++c) {                                                        \
+            T maxval = is_empty ? 0 : -FLT_MAX;                                                       \
+            int maxidx = -1;                                                                          \
+            const T* in = input + ((long)roi_batch_ind * channels + c) * height * width;              \
+            for (int h = hstart; h < hend; ++h)                                                       \
+              for (int w = wstart; w < wend; ++w) {                                                   \
+                int idx = h * width + w;                                                              \
+                if (in[idx] > maxval) { maxval = in[idx]; maxidx = idx; }                             \
+              }                                                                                       \
+            long o = (((long)n * channels + c) * ph_n + ph) * pw_n + pw;                              \
+            output[o] = maxval;                                                                       \
+            argmax[o] = maxidx;                                                                       \
+          }                                                                                           \
+        }                                                                                             \
+    }                                                                                                 \
+  }                                                                                                   \
+  API void oracle_roi_pool_backward_##SFX(const T* grad, const int* argmax, const T* rois,            \
+                                          T* grad_input, int num_rois, int channels, int height,     \
+                                          int width, int ph_n, int pw_n, long n_stride,              \
+                                          long c_stride, long h_stride, long w_stride) {             \
+    /* grad_input must be zero on entry (at::zeros, roi_pool_kernel.cpp:207) */                      \
+    for (int n = 0; n < num_rois; ++n) {                                                              \
+      int roi_batch_ind = (int)rois[n * 5];                                                           \
+      for (int c = 0; c < channels; ++c) {                                                            \
+        T* gi = grad_input + ((long)roi_batch_ind * channels + c) * height * width;                   \
+        const int* am = argmax + ((long)n * channels + c) * ph_n * pw_n;                              \
+        for (int ph = 0; ph < ph_n; ++ph)                                                             \
+          for (int pw = 0; pw < pw_n; ++pw) {                                                         \
+            int a = am[ph * pw_n + pw];                                                               \
+            if (a != -1) gi[a] += grad[n * n_stride + c * c_stride + ph * h_stride + pw * w_stride];  \
+          }                                                                                           \
+      }                                                                                               \
+    }                                                                                                 \
+  }
+
+ORACLE_ROI_POOL(float, f32)
+ORACLE_ROI_POOL(double, f64)

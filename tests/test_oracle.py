@@ -140,3 +140,35 @@ def test_reference_threaded_wrappers_equal_single_thread():
     ga = oracle.roi_align_backward(go, rois, 1.0, 7, 7, 4, 6, 20, 20, 2, True, impl="ref", threads=1)
     gb = oracle.roi_align_backward(go, rois, 1.0, 7, 7, 4, 6, 20, 20, 2, True, impl="ref", threads=4)
     assert torch.equal(ga, gb)
+
+
+# ---- roi_pool -------------------------------------------------------
+def test_roi_pool_golden(golden):
+    """Restatement vs outputs of the reference's own ops.roi_pool + autograd (tests/golden/make_golden_roi_pool.py)."""
+    d = golden("roi_pool.pt")
+    x, rois = d["x"], d["rois"]
+    for c in d["cases"]:
+        out, am = oracle.roi_pool_forward(x, rois, c["ph"], c["pw"], c["scale"])
+        assert torch.equal(out, c["out"]), (c["ph"], c["scale"])
+        gi = oracle.roi_pool_backward(c["grad_out"], rois, am, c["ph"], c["pw"], *x.shape)
+        assert torch.equal(gi, c["grad_in"])
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/libtvref.so not built")
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_roi_pool_restatement_matches_compiled_reference(dtype):
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(3, 5, 17, 23, generator=g, dtype=dtype)
+    K = 50
+    rois = torch.rand(K, 5, generator=g, dtype=dtype) * 30 - 3
+    rois[:, 0] = torch.randint(0, 3, (K,), generator=g).to(dtype)
+    rois[:, 3:] = rois[:, 1:3] + torch.rand(K, 2, generator=g, dtype=dtype) * 25 - 2
+    for scale in (1.0, 0.5, 0.3):
+        for ph, pw in ((4, 6), (1, 1), (7, 7)):
+            a, aa = oracle.roi_pool_forward(x, rois, ph, pw, scale, impl="oracle")
+            b, ab = oracle.roi_pool_forward(x, rois, ph, pw, scale, impl="ref")
+            assert torch.equal(a, b) and torch.equal(aa, ab), (scale, ph, pw)
+            go = torch.randn(K, 5, ph, pw, generator=g, dtype=dtype)
+            go_nc = go.permute(0, 1, 3, 2).contiguous().permute(0, 1, 3, 2)
+            assert torch.equal(oracle.roi_pool_backward(go_nc, rois, aa, ph, pw, 3, 5, 17, 23, impl="oracle"),
+                               oracle.roi_pool_backward(go_nc, rois, ab, ph, pw, 3, 5, 17, 23, impl="ref"))

@@ -550,3 +550,21 @@ def test_nchw_msroi_module_through_relayout(golden):
     for f, w_ in zip(fd.values(), wants):
         assert f.grad.is_contiguous()
         close_bwd(f.grad, w_)
+
+
+def test_box_head_layout_fusion(capi):
+    """Row f2: channels_last pooled features feed fc6 as a view once fc6's columns are permuted."""
+    from cpu_vision_b200 import box_head
+
+    g = torch.Generator().manual_seed(9)
+    N, C, H, W, K, PH = 2, 256, 25, 34, 64, 7
+    x = torch.randn(N, C, H, W, generator=g).to(DEV).contiguous(memory_format=torch.channels_last)
+    rois = rand_rois(g, K, N, W * 32.0, H * 32.0, lo=32.0).to(DEV)
+    y = capi.roi_align_forward(x, rois, PH, PH, 1 / 32, 2, False)
+    flat = box_head.flatten_pooled(y)
+    assert flat.data_ptr() == y.data_ptr() and flat.shape == (K, C * PH * PH)  # a view, not a copy
+    w6 = torch.randn(128, C * PH * PH, generator=g).to(DEV) / 100
+    want = torch.nn.functional.linear(y.contiguous().flatten(1), w6)  # the reference's order
+    got = torch.nn.functional.linear(flat, box_head.fc6_weight_for_channels_last(w6, C, PH, PH))
+    torch.testing.assert_close(got, want, rtol=1e-3, atol=1e-3)
+    assert box_head.flatten_pooled(y.contiguous()).shape == flat.shape
