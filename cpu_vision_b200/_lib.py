@@ -150,3 +150,30 @@ def _register_companions(defined):
             ctx = torch._custom_ops.get_ctx()
             n = ctx.create_unbacked_symint()
             return dets.new_empty((n,), dtype=torch.int64)
+
+    if defined & 4:
+        # csrc/ops/autograd/roi_pool_kernel.cpp:11-152, torchvision/_meta_registrations.py (roi_pool)
+        @lib.register_fake("torchvision::roi_pool")
+        def _(input, rois, spatial_scale, pooled_height, pooled_width):
+            torch._check(rois.size(1) == 5, lambda: "rois must have shape as Tensor[K, 5]")
+            shape = (rois.size(0), input.size(1), pooled_height, pooled_width)
+            return input.new_empty(shape), input.new_empty(shape, dtype=torch.int32)
+
+        @lib.register_fake("torchvision::_roi_pool_backward")
+        def _(grad, rois, argmax, spatial_scale, pooled_height, pooled_width, batch_size, channels, height, width):
+            return grad.new_empty((batch_size, channels, height, width))
+
+        def _pool_setup(ctx, inputs, output):
+            input, rois, scale, ph, pw = inputs
+            ctx.save_for_backward(rois, output[1])
+            ctx.mark_non_differentiable(output[1])
+            ctx.meta = (scale, ph, pw, tuple(input.shape))
+
+        def _pool_backward(ctx, grad, _grad_argmax):
+            rois, argmax = ctx.saved_tensors
+            scale, ph, pw, shape = ctx.meta
+            gi = torch.ops.torchvision._roi_pool_backward(grad, rois, argmax, scale, ph, pw, shape[0], shape[1],
+                                                          shape[2], shape[3])
+            return gi, None, None, None, None
+
+        lib.register_autograd("torchvision::roi_pool", _pool_backward, setup_context=_pool_setup)

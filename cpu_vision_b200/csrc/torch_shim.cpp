@@ -357,8 +357,71 @@ at::Tensor fpn_level_map_cuda(const at::Tensor& rois, int64_t k_min, int64_t k_m
   return levels;
 }
 
+// ---- torchvision::roi_pool ------------------------------------------------
+// cuda/roi_pool_kernel.cu:120-278: same checks and messages; argmax is an int32 tensor with the
+// reference's meaning.  Output and argmax follow the input's memory format.
+std::tuple<at::Tensor, at::Tensor> roi_pool_forward_cuda(const at::Tensor& input, const at::Tensor& rois,
+                                                         double spatial_scale, int64_t pooled_height,
+                                                         int64_t pooled_width) {
+  TORCH_CHECK(input.is_cuda(), "input must be a CUDA tensor");
+  TORCH_CHECK(rois.is_cuda(), "rois must be a CUDA tensor");
+  TORCH_CHECK(rois.size(1) == 5, "Tensor rois should have shape as Tensor[K, 5]");
+  at::TensorArg input_t{input, "input", 1}, rois_t{rois, "rois", 2};
+  at::CheckedFrom c = "roi_pool_forward_kernel";
+  at::checkAllSameGPU(c, {input_t, rois_t});
+  check_roi_dtype(input, rois, c);
+  TORCH_CHECK(input.dim() == 4, "input must be a 4-D tensor [N, C, H, W]");
+  at::cuda::CUDAGuard device_guard(input.device());
+  const int dt = dtype_code(input.scalar_type(), "roi_pool_forward_kernel");
+  const bool nhwc = is_nhwc(input);
+  const at::Tensor input_ = nhwc ? input : input.contiguous();
+  const at::Tensor rois_ = arith_rois(rois, input.scalar_type());
+  const auto mf = nhwc ? at::MemoryFormat::ChannelsLast : at::MemoryFormat::Contiguous;
+  at::Tensor output = at::empty({rois.size(0), input.size(1), pooled_height, pooled_width}, input.options().memory_format(mf));
+  at::Tensor argmax = at::empty({rois.size(0), input.size(1), pooled_height, pooled_width},
+                                input.options().dtype(at::kInt).memory_format(mf));
+  if (output.numel() == 0) return {output, argmax};
+  const int layout = nhwc ? B200DET_NHWC : B200DET_NCHW;
+  check_rc(b200det_roi_pool_forward(input_.data_ptr(), layout, rois_.data_ptr(), output.data_ptr(),
+                                    argmax.data_ptr<int32_t>(), layout, dt, input.size(0), input.size(1), input.size(2),
+                                    input.size(3), rois.size(0), pooled_height, pooled_width, spatial_scale,
+                                    cur_stream()),
+           "roi_pool_forward_kernel");
+  return {output, argmax};
+}
+
+at::Tensor roi_pool_backward_cuda(const at::Tensor& grad, const at::Tensor& rois, const at::Tensor& argmax,
+                                  double spatial_scale, int64_t pooled_height, int64_t pooled_width,
+                                  int64_t batch_size, int64_t channels, int64_t height, int64_t width) {
+  TORCH_CHECK(grad.is_cuda(), "grad must be a CUDA tensor");
+  TORCH_CHECK(rois.is_cuda(), "rois must be a CUDA tensor");
+  TORCH_CHECK(argmax.is_cuda(), "argmax must be a CUDA tensor");
+  at::TensorArg grad_t{grad, "grad", 1}, rois_t{rois, "rois", 2}, argmax_t{argmax, "argmax", 3};
+  at::CheckedFrom c = "roi_pool_backward_kernel";
+  at::checkAllSameGPU(c, {grad_t, rois_t, argmax_t});
+  check_roi_dtype(grad, rois, c);
+  at::cuda::CUDAGuard device_guard(grad.device());
+  const int dt = dtype_code(grad.scalar_type(), "roi_pool_backward_kernel");
+  const bool am_nhwc = is_nhwc(argmax);
+  const at::Tensor argmax_ = (am_nhwc ? argmax : argmax.contiguous()).to(at::kInt);
+  const bool nhwc = am_nhwc;  // grad_input follows the forward's memory format, which argmax recorded
+  at::Tensor grad_input = at::empty(
+      {batch_size, channels, height, width},
+      grad.options().memory_format(nhwc ? at::MemoryFormat::ChannelsLast : at::MemoryFormat::Contiguous));
+  if (grad.numel() == 0) return grad_input.zero_();
+  const at::Tensor rois_ = arith_rois(rois, grad.scalar_type());
+  const int64_t gs[4] = {grad.stride(0), grad.stride(1), grad.stride(2), grad.stride(3)};
+  at::globalContext().alertNotDeterministic("roi_pool_backward_kernel");
+  check_rc(b200det_roi_pool_backward(grad.data_ptr(), gs, argmax_.data_ptr<int32_t>(),
+                                     am_nhwc ? B200DET_NHWC : B200DET_NCHW, rois_.data_ptr(), grad_input.data_ptr(),
+                                     nhwc ? B200DET_NHWC : B200DET_NCHW, dt, batch_size, channels, height, width,
+                                     rois.size(0), pooled_height, pooled_width, cur_stream()),
+           "roi_pool_backward_kernel");
+  return grad_input;
+}
+
 // ---- registration -------------------------------------------------------------------
-int g_defined = 0;  // bit0: we defined the roi_align schemas, bit1: nms
+int g_defined = 0;  // bit0: we defined the roi_align schemas, bit1: nms, bit2: roi_pool
 std::vector<std::unique_ptr<torch::Library>> g_libs;
 
 bool has_schema(const char* name) {
@@ -383,10 +446,22 @@ struct Registrar {
       g_libs.back()->def("nms(Tensor dets, Tensor scores, float iou_threshold) -> Tensor");
       g_defined |= 2;
     }
+    if (!has_schema("torchvision::roi_pool")) {
+      g_libs.emplace_back(new torch::Library(torch::Library::FRAGMENT, "torchvision", std::nullopt, __FILE__, __LINE__));
+      g_libs.back()->def(
+          "roi_pool(Tensor input, Tensor rois, float spatial_scale, SymInt pooled_height, SymInt pooled_width) -> "
+          "(Tensor, Tensor)");
+      g_libs.back()->def(
+          "_roi_pool_backward(Tensor grad, Tensor rois, Tensor argmax, float spatial_scale, SymInt pooled_height, "
+          "SymInt pooled_width, SymInt batch_size, SymInt channels, SymInt height, SymInt width) -> Tensor");
+      g_defined |= 4;
+    }
     g_libs.emplace_back(new torch::Library(torch::Library::IMPL, "torchvision", c10::DispatchKey::CUDA, __FILE__, __LINE__));
     g_libs.back()->impl("roi_align", TORCH_FN(roi_align_forward_cuda));
     g_libs.back()->impl("_roi_align_backward", TORCH_FN(roi_align_backward_cuda));
     g_libs.back()->impl("nms", TORCH_FN(nms_cuda));
+    g_libs.back()->impl("roi_pool", TORCH_FN(roi_pool_forward_cuda));
+    g_libs.back()->impl("_roi_pool_backward", TORCH_FN(roi_pool_backward_cuda));
   }
 };
 Registrar g_registrar;

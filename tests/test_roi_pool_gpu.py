@@ -76,3 +76,26 @@ def test_backward_honours_grad_strides_and_empty(capi):
     assert o0.shape == (0, 8, 4, 6)
     assert torch.equal(capi.roi_pool_backward(go[:0].to(DEV), rois[:0].to(DEV), a0, 4, 6, 2, 8, 20, 20).cpu(),
                        torch.zeros(2, 8, 20, 20))
+
+
+@pytest.mark.parametrize("channels_last", [False, True])
+def test_dispatcher_module_and_autograd(golden, channels_last):
+    """torch.ops.torchvision.roi_pool through the shim, the RoIPool mirror, autograd, list-of-boxes input."""
+    from cpu_vision_b200 import RoIPool
+
+    d = golden("roi_pool.pt")
+    x, rois = d["x"], d["rois"]
+    c = d["cases"][0]
+    xd = _mf(x.to(DEV), channels_last).requires_grad_(True)
+    m = RoIPool((c["ph"], c["pw"]), c["scale"])
+    assert repr(m) == f"RoIPool(output_size=({c['ph']}, {c['pw']}), spatial_scale={c['scale']})"
+    y = m(xd, rois.to(DEV))
+    assert torch.equal(y.detach().cpu().contiguous(), c["out"])
+    y.backward(c["grad_out"].to(DEV))
+    torch.testing.assert_close(xd.grad.cpu().contiguous(), c["grad_in"], rtol=1e-5, atol=1e-5)
+    boxes = [rois[rois[:, 0] == i, 1:].to(DEV) for i in range(2)]
+    order = torch.cat([torch.where(rois[:, 0] == i)[0] for i in range(2)])
+    y2 = m(xd.detach(), boxes)
+    assert torch.equal(y2.cpu().contiguous(), c["out"][order])
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m(x, rois)
