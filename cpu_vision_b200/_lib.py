@@ -177,3 +177,33 @@ def _register_companions(defined):
             return gi, None, None, None, None
 
         lib.register_autograd("torchvision::roi_pool", _pool_backward, setup_context=_pool_setup)
+
+    if defined & 8:
+        # csrc/ops/autograd/ps_roi_pool_kernel.cpp, torchvision/_meta_registrations.py (ps_roi_pool)
+        @lib.register_fake("torchvision::ps_roi_pool")
+        def _(input, rois, spatial_scale, pooled_height, pooled_width):
+            torch._check(rois.size(1) == 5, lambda: "rois must have shape as Tensor[K, 5]")
+            torch._check(input.size(1) % (pooled_height * pooled_width) == 0,
+                         lambda: "input channels must be a multiple of pooling height * pooling width")
+            shape = (rois.size(0), input.size(1) // (pooled_height * pooled_width), pooled_height, pooled_width)
+            return input.new_empty(shape), input.new_empty(shape, dtype=torch.int32)
+
+        @lib.register_fake("torchvision::_ps_roi_pool_backward")
+        def _(grad, rois, channel_mapping, spatial_scale, pooled_height, pooled_width, batch_size, channels, height,
+              width):
+            return grad.new_empty((batch_size, channels, height, width))
+
+        def _ps_setup(ctx, inputs, output):
+            input, rois, scale, ph, pw = inputs
+            ctx.save_for_backward(rois, output[1])
+            ctx.mark_non_differentiable(output[1])
+            ctx.meta = (scale, ph, pw, tuple(input.shape))
+
+        def _ps_backward(ctx, grad, _grad_mapping):
+            rois, mapping = ctx.saved_tensors
+            scale, ph, pw, shape = ctx.meta
+            gi = torch.ops.torchvision._ps_roi_pool_backward(grad, rois, mapping, scale, ph, pw, shape[0], shape[1],
+                                                             shape[2], shape[3])
+            return gi, None, None, None, None
+
+        lib.register_autograd("torchvision::ps_roi_pool", _ps_backward, setup_context=_ps_setup)

@@ -320,4 +320,42 @@ int b200det_roi_pool_backward(const void* grad, const int64_t* grad_strides, con
                            dtype, N, C, H, W, K, (int)PH, (int)PW, (cudaStream_t)stream);
 }
 
+static int ps_check(const char* who, int dtype, int la, int lb, int64_t N, int64_t C, int64_t H, int64_t W, int64_t K,
+                    int64_t PH, int64_t PW) {
+  int rc = check_common(who, dtype, la, lb, N, C, K, PH, PW);
+  if (rc) return rc;
+  if (H < 0 || W < 0 || H > INT32_MAX || W > INT32_MAX) return fail(B200DET_EINVAL, "%s: bad H or W", who);
+  if (PH < 1 || PW < 1 || C % (PH * PW) != 0)
+    return fail(B200DET_EINVAL, "%s: input channels must be a multiple of pooling height * pooling width", who);
+  return 0;
+}
+
+int b200det_ps_roi_pool_forward(const void* input, int in_layout, const void* rois, void* output,
+                                int32_t* channel_mapping, int out_layout, int dtype, int64_t N, int64_t C, int64_t H,
+                                int64_t W, int64_t K, int64_t PH, int64_t PW, double spatial_scale, void* stream) {
+  int rc = ps_check("ps_roi_pool_forward", dtype, in_layout, out_layout, N, C, H, W, K, PH, PW);
+  if (rc) return rc;
+  if (K * C == 0) return 0;
+  if (!rois || !output || !channel_mapping || (!input && N * C * H * W != 0))
+    return fail(B200DET_EINVAL, "ps_roi_pool_forward: null pointer");
+  return ps_roi_pool(true, input, nullptr, in_layout, rois, output, channel_mapping, out_layout, dtype, N, C, H, W, K,
+                     (int)PH, (int)PW, spatial_scale, (cudaStream_t)stream);
+}
+
+int b200det_ps_roi_pool_backward(const void* grad, const int64_t* grad_strides, const int32_t* channel_mapping,
+                                 int mapping_layout, const void* rois, void* grad_input, int gi_layout, int dtype,
+                                 int64_t N, int64_t C, int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+                                 double spatial_scale, void* stream) {
+  int rc = ps_check("ps_roi_pool_backward", dtype, gi_layout, mapping_layout, N, C, H, W, K, PH, PW);
+  if (rc) return rc;
+  if (N * C * H * W == 0) return 0;
+  if (!grad_input) return fail(B200DET_EINVAL, "ps_roi_pool_backward: null grad_input");
+  if (K * C != 0 && (!grad || !grad_strides || !channel_mapping || !rois))
+    return fail(B200DET_EINVAL, "ps_roi_pool_backward: null pointer");
+  static const int64_t zero4[4] = {0, 0, 0, 0};
+  return ps_roi_pool(false, grad, grad_strides ? grad_strides : zero4, gi_layout, rois, grad_input,
+                     const_cast<int32_t*>(channel_mapping), mapping_layout, dtype, N, C, H, W, K, (int)PH, (int)PW,
+                     spatial_scale, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -76,4 +76,9 @@ int roi_pool_backward(const void* grad, const int64_t* gs, const int32_t* argmax
                       void* grad_in, int gi_layout, int dtype, long long N, long long C, long long H, long long W,
                       long long K, int PH, int PW, cudaStream_t st);
 
+// ps_roi_pool_sm100.cu: torchvision::ps_roi_pool (position-sensitive average pooling); see the file for the argument roles
+int ps_roi_pool(bool forward, const void* in_or_grad, const int64_t* gs, int in_layout, const void* rois,
+                void* out_or_gi, int32_t* mapping, int out_layout, int dtype, long long N, long long C, long long H,
+                long long W, long long K, int PH, int PW, double scale, cudaStream_t st);
+
 }  // namespace b200det

@@ -39,3 +39,33 @@ class RoIPool(nn.Module):
 
     def __repr__(self) -> str:
         return f"{self.__class__.__name__}(output_size={self.output_size}, spatial_scale={self.spatial_scale})"
+
+
+def ps_roi_pool(input: Tensor, boxes: Union[Tensor, List[Tensor]], output_size, spatial_scale: float = 1.0) -> Tensor:
+    """Position-sensitive RoI pooling (R-FCN); same arguments and meaning as the reference's ps_roi_pool
+    (torchvision/ops/ps_roi_pool.py:14-49).  Returns Tensor[K, C / (oh * ow), oh, ow]."""
+    _lib.load()
+    check_roi_boxes_shape(boxes)
+    rois = boxes
+    output_size = _pair(output_size)
+    if not isinstance(rois, torch.Tensor):
+        rois = convert_boxes_to_roi_format(rois)
+    if not input.is_cuda:
+        raise RuntimeError("cpu_vision_b200.ps_roi_pool: input must be a CUDA tensor (no CPU fallback)")
+    output, _ = torch.ops.torchvision.ps_roi_pool(input, rois, spatial_scale, output_size[0], output_size[1])
+    return output
+
+
+class PSRoIPool(nn.Module):
+    """See :func:`ps_roi_pool` (reference: ps_roi_pool.py:52-66)."""
+
+    def __init__(self, output_size, spatial_scale: float):
+        super().__init__()
+        self.output_size = output_size
+        self.spatial_scale = spatial_scale
+
+    def forward(self, input: Tensor, rois: Union[Tensor, List[Tensor]]) -> Tensor:
+        return ps_roi_pool(input, rois, self.output_size, self.spatial_scale)
+
+    def __repr__(self) -> str:
+        return f"{self.__class__.__name__}(output_size={self.output_size}, spatial_scale={self.spatial_scale})"

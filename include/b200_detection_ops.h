@@ -252,6 +252,26 @@ int b200det_roi_pool_backward(
     int dtype, int64_t N, int64_t C, int64_t H, int64_t W, int64_t K,
     int64_t PH, int64_t PW, void* stream);
 
+/* torchvision::ps_roi_pool (position-sensitive average pooling, R-FCN).
+ * Replaces ps_roi_pool_forward_kernel / ps_roi_pool_backward_kernel
+ * (torchvision/csrc/ops/cuda/ps_roi_pool_kernel.cu:142-280; CPU twin
+ * cpu/ps_roi_pool_kernel.cpp:148-260).  C must be a multiple of PH * PW; the
+ * output has C / (PH * PW) channels; channel_mapping (int32, output's shape
+ * and layout) records the input channel of every output element.  The
+ * reference clips forward bins to [0, size - 1] and backward bins to
+ * [0, size]; both are kept. */
+int b200det_ps_roi_pool_forward(
+    const void* input, int in_layout, const void* rois, void* output,
+    int32_t* channel_mapping, int out_layout, int dtype, int64_t N, int64_t C,
+    int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+    double spatial_scale, void* stream);
+int b200det_ps_roi_pool_backward(
+    const void* grad, const int64_t* grad_strides,
+    const int32_t* channel_mapping, int mapping_layout, const void* rois,
+    void* grad_input, int gi_layout, int dtype, int64_t N, int64_t C,
+    int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+    double spatial_scale, void* stream);
+
 /* ------------------------------------------------------------------------
  * Host-buffer entry points (what a CPU-tensor caller of the reference binds).
  * Inputs and outputs are HOST pointers; the call stages them through a

@@ -450,3 +450,81 @@ API void oracle_msroi_align_backward_f32(const float* grad, long gs_n, long gs_c
 
 ORACLE_ROI_POOL(float, f32)
 ORACLE_ROI_POOL(double, f64)
+
+/* ---- ps_roi_pool -------------------------------------------------
+ * csrc/ops/cpu/ps_roi_pool_kernel.cpp:14-83 (forward: bins clipped to [0, size - 1]) and :85-146
+ * (backward: roundf, bins clipped to [0, size]), NCHW, same loops. */
+#define ORACLE_PS_ROI_POOL(T, SFX)                                                                     \
+  API void oracle_ps_roi_pool_forward_##SFX(const T* input, const T* rois, T* output, int* mapping,    \
+                                            int num_rois, int channels, int height, int width,         \
+                                            int ph_n, int pw_n, double scale_d) {                      \
+    const T spatial_scale = (T)scale_d;                                                                \
+    const int channels_out = channels / (ph_n * pw_n);                                                 \
+    for (int n = 0; n < num_rois; ++n) {                                                               \
+      const T* r = rois + n * 5;                                                                       \
+      int b = (int)r[0];                                                                               \
+      int sw = (int)round(r[1] * spatial_scale), sh = (int)round(r[2] * spatial_scale);                \
+      int ew = (int)round(r[3] * spatial_scale), eh = (int)round(r[4] * spatial_scale);                \
+      int rw = ew - sw; if (rw < 1) rw = 1;                                                            \
+      int rh = eh - sh; if (rh < 1) rh = 1;                                                            \
+      T bin_h = (T)rh / (T)ph_n, bin_w = (T)rw / (T)pw_n;                                              \
+      int c_in = 0;                                                                                    \
+      for (int c_out = 0; c_out < channels_out; ++c_out)                                               \
+        for (int ph = 0; ph < ph_n; ++ph)                                                              \
+          for (int pw = 0; pw < pw_n; ++pw) {                                                          \
+            int hs = (int)floor((T)ph * bin_h) + sh, ws = (int)floor((T)pw * bin_w) + sw;              \
+            int he = (int)ceil((T)(ph + 1) * bin_h) + sh, we = (int)ceil((T)(pw + 1) * bin_w) + sw;    \
+            hs = hs < 0 ? 0 : (hs > height - 1 ? height - 1 : hs);                                     \
+            he = he < 0 ? 0 : (he > height - 1 ? height - 1 : he);                                     \
+            ws = ws < 0 ? 0 : (ws > width - 1 ? width - 1 : ws);                                       \
+            we = we < 0 ? 0 : (we > width - 1 ? width - 1 : we);                                       \
+            int is_empty = (he <= hs) || (we <= ws);                                                   \
+            const T* in = input + ((long)b * channels + c_in) * height * width;                        \
+            T sum = 0;                                                                                 \
+            for (int h = hs; h < he; ++h)                                                              \
+              for (int w = ws; w < we; ++w) sum += in[h * width + w];                                  \
+            long o = (((long)n * channels_out + c_out) * ph_n + ph) * pw_n + pw;                       \
+            T area = (T)((he - hs) * (we - ws));                                                       \
+            output[o] = is_empty ? (T)0 : sum / area;                                                  \
+            mapping[o] = c_in;                                                                         \
+            c_in++;                                                                                    \
+          }                                                                                            \
+    }                                                                                                  \
+  }                                                                                                    \
+  API void oracle_ps_roi_pool_backward_##SFX(const T* grad, const int* mapping, const T* rois,         \
+                                             T* grad_input, int num_rois, int channels, int height,    \
+                                             int width, int ph_n, int pw_n, double scale_d) {          \
+    const T spatial_scale = (T)scale_d;                                                                \
+    const int channels_out = channels / (ph_n * pw_n);                                                 \
+    for (int n = 0; n < num_rois; ++n) {                                                               \
+      const T* r = rois + n * 5;                                                                       \
+      int b = (int)r[0];                                                                               \
+      int sw = (int)roundf(r[1] * spatial_scale), sh = (int)roundf(r[2] * spatial_scale);              \
+      int ew = (int)roundf(r[3] * spatial_scale), eh = (int)roundf(r[4] * spatial_scale);              \
+      int rw = ew - sw; if (rw < 1) rw = 1;                                                            \
+      int rh = eh - sh; if (rh < 1) rh = 1;                                                            \
+      T bin_h = (T)rh / (T)ph_n, bin_w = (T)rw / (T)pw_n;                                              \
+      for (int ph = 0; ph < ph_n; ++ph)                                                                \
+        for (int pw = 0; pw < pw_n; ++pw) {                                                            \
+          int hs = (int)floor((T)ph * bin_h) + sh, ws = (int)floor((T)pw * bin_w) + sw;                \
+          int he = (int)ceil((T)(ph + 1) * bin_h) + sh, we = (int)ceil((T)(pw + 1) * bin_w) + sw;      \
+          hs = hs < 0 ? 0 : (hs > height ? height : hs);                                               \
+          he = he < 0 ? 0 : (he > height ? height : he);                                               \
+          ws = ws < 0 ? 0 : (ws > width ? width : ws);                                                 \
+          we = we < 0 ? 0 : (we > width ? width : we);                                                 \
+          int is_empty = (he <= hs) || (we <= ws);                                                     \
+          for (int c_out = 0; c_out < channels_out; ++c_out) {                                         \
+            long o = (((long)n * channels_out + c_out) * ph_n + ph) * pw_n + pw;                       \
+            int c_in = mapping[o];                                                                     \
+            T* gi = grad_input + ((long)b * channels + c_in) * height * width;                         \
+            T area = (T)((he - hs) * (we - ws));                                                       \
+            T diff = is_empty ? (T)0 : grad[o] / area;                                                 \
+            for (int h = hs; h < he; ++h)                                                              \
+              for (int w = ws; w < we; ++w) gi[h * width + w] += diff;                                 \
+          }                                                                                            \
+        }                                                                                              \
+    }                                                                                                  \
+  }
+
+ORACLE_PS_ROI_POOL(float, f32)
+ORACLE_PS_ROI_POOL(double, f64)

@@ -1,5 +1,5 @@
-"""Generates tests/golden/roi_pool.pt from the REFERENCE's own torchvision.ops.roi_pool (compiled CPU kernels,
-autograd included), built in /tmp by make_golden.build_reference.
+"""Generates tests/golden/roi_pool.pt and ps_roi_pool.pt from the REFERENCE's own torchvision.ops.roi_pool /
+ps_roi_pool (compiled CPU kernels, autograd included), built in /tmp by make_golden.build_reference.
 
     python tests/golden/make_golden_roi_pool.py
 """
@@ -37,6 +37,18 @@ for (ph, pw) in ((7, 7), (3, 5), (1, 1)):
         cases.append(dict(ph=ph, pw=pw, scale=scale, out=y.detach().clone(), grad_out=gy, grad_in=xi.grad.clone()))
 torch.save(dict(x=x, rois=rois, cases=cases), "%(out)s/roi_pool.pt")
 print("roi_pool golden written", len(cases))
+# ---- ps_roi_pool: channels must be a multiple of PH * PW
+pcases = []
+for (ph, pw, cmul) in ((3, 3, 2), (2, 4, 3), (1, 1, 5)):
+    xp = torch.randn(2, cmul * ph * pw, 23, 31, generator=g)
+    for scale in (0.25, 1.0 / 3.0):
+        xi = xp.clone().requires_grad_(True)
+        y = ops.ps_roi_pool(xi, rois, (ph, pw), scale)
+        gy = torch.randn(y.shape, generator=g)
+        y.backward(gy)
+        pcases.append(dict(ph=ph, pw=pw, scale=scale, x=xp, out=y.detach().clone(), grad_out=gy, grad_in=xi.grad.clone()))
+torch.save(dict(rois=rois, cases=pcases), "%(out)s/ps_roi_pool.pt")
+print("ps_roi_pool golden written", len(pcases))
 '''
 
 

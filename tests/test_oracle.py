@@ -172,3 +172,31 @@ def test_roi_pool_restatement_matches_compiled_reference(dtype):
             go_nc = go.permute(0, 1, 3, 2).contiguous().permute(0, 1, 3, 2)
             assert torch.equal(oracle.roi_pool_backward(go_nc, rois, aa, ph, pw, 3, 5, 17, 23, impl="oracle"),
                                oracle.roi_pool_backward(go_nc, rois, ab, ph, pw, 3, 5, 17, 23, impl="ref"))
+
+
+def test_ps_roi_pool_golden(golden):
+    d = golden("ps_roi_pool.pt")
+    for c in d["cases"]:
+        out, cm = oracle.ps_roi_pool_forward(c["x"], d["rois"], c["ph"], c["pw"], c["scale"])
+        assert torch.equal(out, c["out"]), (c["ph"], c["scale"])
+        gi = oracle.ps_roi_pool_backward(c["grad_out"], d["rois"], cm, c["scale"], c["ph"], c["pw"], *c["x"].shape)
+        assert torch.equal(gi, c["grad_in"])
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/libtvref.so not built")
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_ps_roi_pool_restatement_matches_compiled_reference(dtype):
+    g = torch.Generator().manual_seed(13)
+    K = 50
+    rois = torch.rand(K, 5, generator=g, dtype=dtype) * 30 - 3
+    rois[:, 0] = torch.randint(0, 3, (K,), generator=g).to(dtype)
+    rois[:, 3:] = rois[:, 1:3] + torch.rand(K, 2, generator=g, dtype=dtype) * 25 - 2
+    for ph, pw, cm_ in ((2, 3, 2), (1, 1, 4), (3, 3, 1)):
+        x = torch.randn(3, cm_ * ph * pw, 17, 23, generator=g, dtype=dtype)
+        for scale in (1.0, 0.5, 0.3):
+            a, ma = oracle.ps_roi_pool_forward(x, rois, ph, pw, scale, impl="oracle")
+            b, mb = oracle.ps_roi_pool_forward(x, rois, ph, pw, scale, impl="ref")
+            assert torch.equal(a, b) and torch.equal(ma, mb), (scale, ph, pw)
+            go = torch.randn(a.shape, generator=g, dtype=dtype)
+            assert torch.equal(oracle.ps_roi_pool_backward(go, rois, ma, scale, ph, pw, *x.shape, impl="oracle"),
+                               oracle.ps_roi_pool_backward(go, rois, mb, scale, ph, pw, *x.shape, impl="ref"))
