@@ -207,3 +207,33 @@ def _register_companions(defined):
             return gi, None, None, None, None
 
         lib.register_autograd("torchvision::ps_roi_pool", _ps_backward, setup_context=_ps_setup)
+
+    if defined & 16:
+        # csrc/ops/autograd/ps_roi_align_kernel.cpp, torchvision/_meta_registrations.py (ps_roi_align)
+        @lib.register_fake("torchvision::ps_roi_align")
+        def _(input, rois, spatial_scale, pooled_height, pooled_width, sampling_ratio):
+            torch._check(rois.size(1) == 5, lambda: "rois must have shape as Tensor[K, 5]")
+            torch._check(input.size(1) % (pooled_height * pooled_width) == 0,
+                         lambda: "input channels must be a multiple of pooling height * pooling width")
+            shape = (rois.size(0), input.size(1) // (pooled_height * pooled_width), pooled_height, pooled_width)
+            return input.new_empty(shape), input.new_empty(shape, dtype=torch.int32)
+
+        @lib.register_fake("torchvision::_ps_roi_align_backward")
+        def _(grad, rois, channel_mapping, spatial_scale, pooled_height, pooled_width, sampling_ratio, batch_size,
+              channels, height, width):
+            return grad.new_empty((batch_size, channels, height, width))
+
+        def _psa_setup(ctx, inputs, output):
+            input, rois, scale, ph, pw, sr = inputs
+            ctx.save_for_backward(rois, output[1])
+            ctx.mark_non_differentiable(output[1])
+            ctx.meta = (scale, ph, pw, sr, tuple(input.shape))
+
+        def _psa_backward(ctx, grad, _grad_mapping):
+            rois, mapping = ctx.saved_tensors
+            scale, ph, pw, sr, shape = ctx.meta
+            gi = torch.ops.torchvision._ps_roi_align_backward(grad, rois, mapping, scale, ph, pw, sr, shape[0],
+                                                              shape[1], shape[2], shape[3])
+            return gi, None, None, None, None, None
+
+        lib.register_autograd("torchvision::ps_roi_align", _psa_backward, setup_context=_psa_setup)

@@ -28,7 +28,7 @@ SYMBOLS = [
     "b200det_nms_host", "b200det_batched_nms_host", "b200det_host_release",
     "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented", "b200det_clip_filter_boxes", "b200det_relayout",
     "b200det_roi_pool_forward", "b200det_roi_pool_backward", "b200det_ps_roi_pool_forward",
-    "b200det_ps_roi_pool_backward",
+    "b200det_ps_roi_pool_backward", "b200det_ps_roi_align_forward", "b200det_ps_roi_align_backward",
 ]
 
 _declared = False
@@ -70,6 +70,9 @@ def lib():
         l.b200det_roi_pool_backward.argtypes = [_P, _P, _P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _P]
         l.b200det_ps_roi_pool_forward.argtypes = [_P, _I, _P, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _P]
         l.b200det_ps_roi_pool_backward.argtypes = [_P, _P, _P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _P]
+        l.b200det_ps_roi_align_forward.argtypes = [_P, _I, _P, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I, _P]
+        l.b200det_ps_roi_align_backward.argtypes = [_P, _P, _P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I,
+                                                    _P]
         _declared = True
     return l
 
@@ -370,6 +373,36 @@ def ps_roi_pool_backward(grad, rois, mapping, spatial_scale, pooled_h, pooled_w,
                                                   r.data_ptr(), gi.data_ptr(), layout, _dt(grad), N, Cc, H, W,
                                                   r.shape[0], pooled_h, pooled_w, float(spatial_scale), _stream(grad)),
                "b200det_ps_roi_pool_backward")
+    return gi
+
+
+def ps_roi_align_forward(x, rois, pooled_h, pooled_w, spatial_scale=1.0, sampling_ratio=-1):
+    """(output [K, C/(PH*PW), PH, PW], channel_mapping int32) in x's memory format."""
+    layout, x = _layout_of(x)
+    r = _arith(rois, x.dtype)
+    N, Cc, H, W = x.shape
+    K = r.shape[0]
+    out = _empty_like_layout((K, Cc // (pooled_h * pooled_w), pooled_h, pooled_w), x, layout)
+    cm = torch.empty_like(out, dtype=torch.int32)
+    with torch.cuda.device(x.device):
+        _check(lib().b200det_ps_roi_align_forward(x.data_ptr(), layout, r.data_ptr(), out.data_ptr(), cm.data_ptr(),
+                                                  layout, _dt(x), N, Cc, H, W, K, pooled_h, pooled_w,
+                                                  float(spatial_scale), int(sampling_ratio), _stream(x)),
+               "b200det_ps_roi_align_forward")
+    return out, cm
+
+
+def ps_roi_align_backward(grad, rois, mapping, spatial_scale, pooled_h, pooled_w, sampling_ratio, N, Cc, H, W,
+                          layout=NCHW):
+    r = _arith(rois, grad.dtype)
+    cm_layout, cm = _layout_of(mapping)
+    gi = _empty_like_layout((N, Cc, H, W), grad, layout)
+    with torch.cuda.device(grad.device):
+        _check(lib().b200det_ps_roi_align_backward(grad.data_ptr(), _strides(grad), cm.data_ptr(), cm_layout,
+                                                   r.data_ptr(), gi.data_ptr(), layout, _dt(grad), N, Cc, H, W,
+                                                   r.shape[0], pooled_h, pooled_w, float(spatial_scale),
+                                                   int(sampling_ratio), _stream(grad)),
+               "b200det_ps_roi_align_backward")
     return gi
 
 

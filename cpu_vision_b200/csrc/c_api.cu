@@ -358,4 +358,33 @@ int b200det_ps_roi_pool_backward(const void* grad, const int64_t* grad_strides, 
                      spatial_scale, (cudaStream_t)stream);
 }
 
+int b200det_ps_roi_align_forward(const void* input, int in_layout, const void* rois, void* output,
+                                 int32_t* channel_mapping, int out_layout, int dtype, int64_t N, int64_t C, int64_t H,
+                                 int64_t W, int64_t K, int64_t PH, int64_t PW, double spatial_scale,
+                                 int sampling_ratio, void* stream) {
+  int rc = ps_check("ps_roi_align_forward", dtype, in_layout, out_layout, N, C, H, W, K, PH, PW);
+  if (rc) return rc;
+  if (K * C == 0) return 0;
+  if (!rois || !output || !channel_mapping || (!input && N * C * H * W != 0))
+    return fail(B200DET_EINVAL, "ps_roi_align_forward: null pointer");
+  return ps_roi_align(true, input, nullptr, in_layout, rois, output, channel_mapping, out_layout, dtype, N, C, H, W, K,
+                      (int)PH, (int)PW, spatial_scale, sampling_ratio, (cudaStream_t)stream);
+}
+
+int b200det_ps_roi_align_backward(const void* grad, const int64_t* grad_strides, const int32_t* channel_mapping,
+                                  int mapping_layout, const void* rois, void* grad_input, int gi_layout, int dtype,
+                                  int64_t N, int64_t C, int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+                                  double spatial_scale, int sampling_ratio, void* stream) {
+  int rc = ps_check("ps_roi_align_backward", dtype, gi_layout, mapping_layout, N, C, H, W, K, PH, PW);
+  if (rc) return rc;
+  if (N * C * H * W == 0) return 0;
+  if (!grad_input) return fail(B200DET_EINVAL, "ps_roi_align_backward: null grad_input");
+  if (K * C != 0 && (!grad || !grad_strides || !channel_mapping || !rois))
+    return fail(B200DET_EINVAL, "ps_roi_align_backward: null pointer");
+  static const int64_t zero4[4] = {0, 0, 0, 0};
+  return ps_roi_align(false, grad, grad_strides ? grad_strides : zero4, gi_layout, rois, grad_input,
+                      const_cast<int32_t*>(channel_mapping), mapping_layout, dtype, N, C, H, W, K, (int)PH, (int)PW,
+                      spatial_scale, sampling_ratio, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -81,4 +81,9 @@ int ps_roi_pool(bool forward, const void* in_or_grad, const int64_t* gs, int in_
                 void* out_or_gi, int32_t* mapping, int out_layout, int dtype, long long N, long long C, long long H,
                 long long W, long long K, int PH, int PW, double scale, cudaStream_t st);
 
+// ps_roi_align_sm100.cu: torchvision::ps_roi_align; argument roles as ps_roi_pool
+int ps_roi_align(bool forward, const void* in_or_grad, const int64_t* gs, int in_layout, const void* rois,
+                 void* out_or_gi, int32_t* mapping, int out_layout, int dtype, long long N, long long C, long long H,
+                 long long W, long long K, int PH, int PW, double scale, int sr, cudaStream_t st);
+
 }  // namespace b200det

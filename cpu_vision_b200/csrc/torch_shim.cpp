@@ -484,8 +484,74 @@ at::Tensor ps_roi_pool_backward_cuda(const at::Tensor& grad, const at::Tensor& r
   return grad_input;
 }
 
+// ---- torchvision::ps_roi_align --------------------------------------------
+// cuda/ps_roi_align_kernel.cu:293-444: same checks and messages.
+std::tuple<at::Tensor, at::Tensor> ps_roi_align_forward_cuda(const at::Tensor& input, const at::Tensor& rois,
+                                                             double spatial_scale, int64_t pooled_height,
+                                                             int64_t pooled_width, int64_t sampling_ratio) {
+  TORCH_CHECK(input.is_cuda(), "input must be a CUDA tensor");
+  TORCH_CHECK(rois.is_cuda(), "rois must be a CUDA tensor");
+  TORCH_CHECK(rois.size(1) == 5, "Tensor rois should have shape as Tensor[K, 5]");
+  at::TensorArg input_t{input, "input", 1}, rois_t{rois, "rois", 2};
+  at::CheckedFrom c = "ps_roi_align_forward_kernel";
+  at::checkAllSameGPU(c, {input_t, rois_t});
+  check_roi_dtype(input, rois, c);
+  TORCH_CHECK(input.dim() == 4, "input must be a 4-D tensor [N, C, H, W]");
+  TORCH_CHECK(pooled_height > 0 && pooled_width > 0 && input.size(1) % (pooled_height * pooled_width) == 0,
+              "input channels must be a multiple of pooling height * pooling width");
+  at::cuda::CUDAGuard device_guard(input.device());
+  const int dt = dtype_code(input.scalar_type(), "ps_roi_align_forward_kernel");
+  const bool nhwc = is_nhwc(input);
+  const at::Tensor input_ = nhwc ? input : input.contiguous();
+  const at::Tensor rois_ = arith_rois(rois, input.scalar_type());
+  const auto mf = nhwc ? at::MemoryFormat::ChannelsLast : at::MemoryFormat::Contiguous;
+  const int64_t c_out = input.size(1) / (pooled_height * pooled_width);
+  at::Tensor output = at::empty({rois.size(0), c_out, pooled_height, pooled_width}, input.options().memory_format(mf));
+  at::Tensor mapping = at::empty({rois.size(0), c_out, pooled_height, pooled_width},
+                                 input.options().dtype(at::kInt).memory_format(mf));
+  if (output.numel() == 0) return {output, mapping};
+  const int layout = nhwc ? B200DET_NHWC : B200DET_NCHW;
+  check_rc(b200det_ps_roi_align_forward(input_.data_ptr(), layout, rois_.data_ptr(), output.data_ptr(),
+                                        mapping.data_ptr<int32_t>(), layout, dt, input.size(0), input.size(1),
+                                        input.size(2), input.size(3), rois.size(0), pooled_height, pooled_width,
+                                        spatial_scale, (int)sampling_ratio, cur_stream()),
+           "ps_roi_align_forward_kernel");
+  return {output, mapping};
+}
+
+at::Tensor ps_roi_align_backward_cuda(const at::Tensor& grad, const at::Tensor& rois, const at::Tensor& channel_mapping,
+                                      double spatial_scale, int64_t pooled_height, int64_t pooled_width,
+                                      int64_t sampling_ratio, int64_t batch_size, int64_t channels, int64_t height,
+                                      int64_t width) {
+  TORCH_CHECK(grad.is_cuda(), "grad must be a CUDA tensor");
+  TORCH_CHECK(rois.is_cuda(), "rois must be a CUDA tensor");
+  TORCH_CHECK(channel_mapping.is_cuda(), "channel_mapping must be a CUDA tensor");
+  at::TensorArg grad_t{grad, "grad", 1}, rois_t{rois, "rois", 2}, cm_t{channel_mapping, "channel_mapping", 3};
+  at::CheckedFrom c = "ps_roi_align_backward_kernel";
+  at::checkAllSameGPU(c, {grad_t, rois_t, cm_t});
+  check_roi_dtype(grad, rois, c);
+  at::cuda::CUDAGuard device_guard(grad.device());
+  const int dt = dtype_code(grad.scalar_type(), "ps_roi_align_backward_kernel");
+  const bool nhwc = is_nhwc(channel_mapping);
+  const at::Tensor cm_ = (nhwc ? channel_mapping : channel_mapping.contiguous()).to(at::kInt);
+  at::Tensor grad_input = at::empty(
+      {batch_size, channels, height, width},
+      grad.options().memory_format(nhwc ? at::MemoryFormat::ChannelsLast : at::MemoryFormat::Contiguous));
+  if (grad.numel() == 0) return grad_input.zero_();
+  const at::Tensor rois_ = arith_rois(rois, grad.scalar_type());
+  const int64_t gs[4] = {grad.stride(0), grad.stride(1), grad.stride(2), grad.stride(3)};
+  at::globalContext().alertNotDeterministic("ps_roi_align_backward_kernel");
+  const int layout = nhwc ? B200DET_NHWC : B200DET_NCHW;
+  check_rc(b200det_ps_roi_align_backward(grad.data_ptr(), gs, cm_.data_ptr<int32_t>(), layout, rois_.data_ptr(),
+                                         grad_input.data_ptr(), layout, dt, batch_size, channels, height, width,
+                                         rois.size(0), pooled_height, pooled_width, spatial_scale,
+                                         (int)sampling_ratio, cur_stream()),
+           "ps_roi_align_backward_kernel");
+  return grad_input;
+}
+
 // ---- registration -------------------------------------------------------------------
-int g_defined = 0;  // bit0: we defined the roi_align schemas, bit1: nms, bit2: roi_pool, bit3: ps_roi_pool
+int g_defined = 0;  // bit0: we defined the roi_align schemas, bit1: nms, bit2: roi_pool, bit3: ps_roi_pool, bit4: ps_roi_align
 std::vector<std::unique_ptr<torch::Library>> g_libs;
 
 bool has_schema(const char* name) {
@@ -530,6 +596,17 @@ struct Registrar {
           "pooled_height, SymInt pooled_width, SymInt batch_size, SymInt channels, SymInt height, SymInt width) -> Tensor");
       g_defined |= 8;
     }
+    if (!has_schema("torchvision::ps_roi_align")) {
+      g_libs.emplace_back(new torch::Library(torch::Library::FRAGMENT, "torchvision", std::nullopt, __FILE__, __LINE__));
+      g_libs.back()->def(
+          "ps_roi_align(Tensor input, Tensor rois, float spatial_scale, SymInt pooled_height, SymInt pooled_width, "
+          "int sampling_ratio) -> (Tensor, Tensor)");
+      g_libs.back()->def(
+          "_ps_roi_align_backward(Tensor grad, Tensor rois, Tensor channel_mapping, float spatial_scale, SymInt "
+          "pooled_height, SymInt pooled_width, int sampling_ratio, SymInt batch_size, SymInt channels, SymInt height, "
+          "SymInt width) -> Tensor");
+      g_defined |= 16;
+    }
     g_libs.emplace_back(new torch::Library(torch::Library::IMPL, "torchvision", c10::DispatchKey::CUDA, __FILE__, __LINE__));
     g_libs.back()->impl("roi_align", TORCH_FN(roi_align_forward_cuda));
     g_libs.back()->impl("_roi_align_backward", TORCH_FN(roi_align_backward_cuda));
@@ -538,6 +615,8 @@ struct Registrar {
     g_libs.back()->impl("_roi_pool_backward", TORCH_FN(roi_pool_backward_cuda));
     g_libs.back()->impl("ps_roi_pool", TORCH_FN(ps_roi_pool_forward_cuda));
     g_libs.back()->impl("_ps_roi_pool_backward", TORCH_FN(ps_roi_pool_backward_cuda));
+    g_libs.back()->impl("ps_roi_align", TORCH_FN(ps_roi_align_forward_cuda));
+    g_libs.back()->impl("_ps_roi_align_backward", TORCH_FN(ps_roi_align_backward_cuda));
   }
 };
 Registrar g_registrar;

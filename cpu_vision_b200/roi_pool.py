@@ -69,3 +69,37 @@ class PSRoIPool(nn.Module):
 
     def __repr__(self) -> str:
         return f"{self.__class__.__name__}(output_size={self.output_size}, spatial_scale={self.spatial_scale})"
+
+
+def ps_roi_align(input: Tensor, boxes: Union[Tensor, List[Tensor]], output_size, spatial_scale: float = 1.0,
+                 sampling_ratio: int = -1) -> Tensor:
+    """Position-sensitive RoIAlign (Light-Head R-CNN); same arguments and meaning as the reference's ps_roi_align
+    (torchvision/ops/ps_roi_align.py:14-62).  Returns Tensor[K, C / (oh * ow), oh, ow]."""
+    _lib.load()
+    check_roi_boxes_shape(boxes)
+    rois = boxes
+    output_size = _pair(output_size)
+    if not isinstance(rois, torch.Tensor):
+        rois = convert_boxes_to_roi_format(rois)
+    if not input.is_cuda:
+        raise RuntimeError("cpu_vision_b200.ps_roi_align: input must be a CUDA tensor (no CPU fallback)")
+    output, _ = torch.ops.torchvision.ps_roi_align(input, rois, spatial_scale, output_size[0], output_size[1],
+                                                   sampling_ratio)
+    return output
+
+
+class PSRoIAlign(nn.Module):
+    """See :func:`ps_roi_align` (reference: ps_roi_align.py:65-90)."""
+
+    def __init__(self, output_size, spatial_scale: float, sampling_ratio: int):
+        super().__init__()
+        self.output_size = output_size
+        self.spatial_scale = spatial_scale
+        self.sampling_ratio = sampling_ratio
+
+    def forward(self, input: Tensor, rois: Union[Tensor, List[Tensor]]) -> Tensor:
+        return ps_roi_align(input, rois, self.output_size, self.spatial_scale, self.sampling_ratio)
+
+    def __repr__(self) -> str:
+        return (f"{self.__class__.__name__}(output_size={self.output_size}, spatial_scale={self.spatial_scale}, "
+                f"sampling_ratio={self.sampling_ratio})")

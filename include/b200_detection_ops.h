@@ -272,6 +272,24 @@ int b200det_ps_roi_pool_backward(
     int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
     double spatial_scale, void* stream);
 
+/* torchvision::ps_roi_align (position-sensitive RoIAlign).  Replaces
+ * ps_roi_align_forward_kernel / ps_roi_align_backward_kernel
+ * (torchvision/csrc/ops/cuda/ps_roi_align_kernel.cu:293-444; CPU twin
+ * cpu/ps_roi_align_kernel.cpp:302-431).  Geometry of roi_align with
+ * aligned = 1 and no size clamp; count = grid_h * grid_w (no max(., 1)).
+ * Arguments as b200det_ps_roi_pool_*, plus sampling_ratio (<= 0: adaptive). */
+int b200det_ps_roi_align_forward(
+    const void* input, int in_layout, const void* rois, void* output,
+    int32_t* channel_mapping, int out_layout, int dtype, int64_t N, int64_t C,
+    int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+    double spatial_scale, int sampling_ratio, void* stream);
+int b200det_ps_roi_align_backward(
+    const void* grad, const int64_t* grad_strides,
+    const int32_t* channel_mapping, int mapping_layout, const void* rois,
+    void* grad_input, int gi_layout, int dtype, int64_t N, int64_t C,
+    int64_t H, int64_t W, int64_t K, int64_t PH, int64_t PW,
+    double spatial_scale, int sampling_ratio, void* stream);
+
 /* ------------------------------------------------------------------------
  * Host-buffer entry points (what a CPU-tensor caller of the reference binds).
  * Inputs and outputs are HOST pointers; the call stages them through a

@@ -76,6 +76,12 @@ def _declare(l, impl):
         f = getattr(l, f"{pre}_ps_roi_pool_backward_{sfx}")
         f.argtypes = [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _D]
         f.restype = None
+        f = getattr(l, f"{pre}_ps_roi_align_forward_{sfx}")
+        f.argtypes = [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _D, _I]
+        f.restype = None
+        f = getattr(l, f"{pre}_ps_roi_align_backward_{sfx}")
+        f.argtypes = [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _D, _I]
+        f.restype = None
     if impl == "oracle":
         for name in ("oracle_batched_nms_trick_f32", "oracle_batched_nms_vanilla_f32"):
             f = getattr(l, name)
@@ -286,4 +292,37 @@ def ps_roi_pool_backward(grad, rois, mapping, spatial_scale, pooled_h, pooled_w,
         getattr(lib(impl), f"{pre}_ps_roi_pool_backward_{_sfx(grad)}")(grad.data_ptr(), cm.data_ptr(), rois.data_ptr(),
                                                                        gi.data_ptr(), rois.shape[0], Cc, H, W,
                                                                        pooled_h, pooled_w, float(spatial_scale))
+    return gi
+
+
+def ps_roi_align_forward(x, rois, pooled_h, pooled_w, spatial_scale=1.0, sampling_ratio=-1, impl="oracle"):
+    """cpu/ps_roi_align_kernel.cpp:302-365 -> (output [K, C/(PH*PW), PH, PW], channel_mapping int32), NCHW."""
+    x = _cpu(x).contiguous()
+    rois = _cpu(rois).to(x.dtype).contiguous()
+    N, Cc, H, W = x.shape
+    K = rois.shape[0]
+    co = Cc // (pooled_h * pooled_w)
+    out = torch.zeros(K, co, pooled_h, pooled_w, dtype=x.dtype)
+    cm = torch.zeros(K, co, pooled_h, pooled_w, dtype=torch.int32)
+    pre = "oracle" if impl == "oracle" else "tvref"
+    if out.numel():
+        getattr(lib(impl), f"{pre}_ps_roi_align_forward_{_sfx(x)}")(x.data_ptr(), rois.data_ptr(), out.data_ptr(),
+                                                                    cm.data_ptr(), K, Cc, H, W, pooled_h, pooled_w,
+                                                                    float(spatial_scale), int(sampling_ratio))
+    return out, cm
+
+
+def ps_roi_align_backward(grad, rois, mapping, spatial_scale, pooled_h, pooled_w, sampling_ratio, N, Cc, H, W,
+                          impl="oracle"):
+    """cpu/ps_roi_align_kernel.cpp:367-431 (grad.contiguous() like the reference)."""
+    grad = _cpu(grad).contiguous()
+    rois = _cpu(rois).to(grad.dtype).contiguous()
+    cm = _cpu(mapping).to(torch.int32).contiguous()
+    gi = torch.zeros(N, Cc, H, W, dtype=grad.dtype)
+    pre = "oracle" if impl == "oracle" else "tvref"
+    if grad.numel():
+        getattr(lib(impl), f"{pre}_ps_roi_align_backward_{_sfx(grad)}")(grad.data_ptr(), cm.data_ptr(), rois.data_ptr(),
+                                                                        gi.data_ptr(), rois.shape[0], Cc, H, W,
+                                                                        pooled_h, pooled_w, float(spatial_scale),
+                                                                        int(sampling_ratio))
     return gi

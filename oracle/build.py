@@ -7,7 +7,7 @@ Outputs (both git-ignored, both travel to the GPU box with the gpurun snapshot):
   oracle/liboracle.so       gcc build of oracle/detection_oracle.c (the restatement)
   oracle/_ref/libtvref.so   the reference's own cpu/roi_align_kernel.cpp,
                             cpu/nms_kernel.cpp, cpu/roi_pool_kernel.cpp and
-                            cpu/ps_roi_pool_kernel.cpp, compiled from /root/reference where
+                            cpu/ps_roi_pool_kernel.cpp, cpu/ps_roi_align_kernel.cpp, compiled from /root/reference where
                             they lie via oracle/ref_wrap.cpp.  Only built when
                             /root/reference exists (it does not on the GPU box; the
                             prebuilt file is used there).
@@ -43,13 +43,14 @@ def build_ref(force=False):
     out = os.path.join(out_dir, "libtvref.so")
     ref_srcs = [os.path.join(REFERENCE, "torchvision/csrc/ops/cpu", f)
                 for f in ("roi_align_kernel.cpp", "roi_align_common.h", "nms_kernel.cpp", "roi_pool_kernel.cpp",
-                          "ps_roi_pool_kernel.cpp")]
+                          "ps_roi_pool_kernel.cpp", "ps_roi_align_kernel.cpp")]
     if not all(os.path.exists(s) for s in ref_srcs):
         return out if os.path.exists(out) else None
     wrap = os.path.join(HERE, "ref_wrap.cpp")
     wrap_pool = os.path.join(HERE, "ref_wrap_roi_pool.cpp")
     wrap_ps = os.path.join(HERE, "ref_wrap_ps_roi_pool.cpp")
-    if not (force or _stale(out, [wrap, wrap_pool, wrap_ps] + ref_srcs)):
+    wrap_psa = os.path.join(HERE, "ref_wrap_ps_roi_align.cpp")
+    if not (force or _stale(out, [wrap, wrap_pool, wrap_ps, wrap_psa] + ref_srcs)):
         return out
     import torch
     from torch.utils import cpp_extension as ce
@@ -60,7 +61,7 @@ def build_ref(force=False):
            "-D_GLIBCXX_USE_CXX11_ABI=%d" % int(torch._C._GLIBCXX_USE_CXX11_ABI),
            "-I" + REFERENCE]
     cmd += ["-I" + p for p in ce.include_paths()]
-    cmd += [wrap, wrap_pool, wrap_ps, "-o", out, "-L" + torch_lib, "-ltorch", "-ltorch_cpu", "-lc10",
+    cmd += [wrap, wrap_pool, wrap_ps, wrap_psa, "-o", out, "-L" + torch_lib, "-ltorch", "-ltorch_cpu", "-lc10",
             "-Wl,-rpath," + torch_lib, "-pthread"]
     subprocess.check_call(cmd)
     return out

@@ -528,3 +528,105 @@ ORACLE_ROI_POOL(double, f64)
 
 ORACLE_PS_ROI_POOL(float, f32)
 ORACLE_PS_ROI_POOL(double, f64)
+
+/* ---- ps_roi_align ------------------------------------------------
+ * csrc/ops/cpu/ps_roi_align_kernel.cpp:9-60 (bilinear_interpolate), :62-140 (forward),
+ * :142-300 (gradient weights + backward), NCHW, same loops and operation order. */
+#define ORACLE_PS_ROI_ALIGN(T, SFX)                                                                    \
+  static T ps_bilinear_##SFX(const T* in, int height, int width, T y, T x) {                           \
+    if (y < -1.0 || y > height || x < -1.0 || x > width) return 0;                                     \
+    if (y <= 0) y = 0;                                                                                 \
+    if (x <= 0) x = 0;                                                                                 \
+    int y_low = (int)y, x_low = (int)x, y_high, x_high;                                                \
+    if (y_low >= height - 1) { y_high = y_low = height - 1; y = (T)y_low; } else y_high = y_low + 1;   \
+    if (x_low >= width - 1) { x_high = x_low = width - 1; x = (T)x_low; } else x_high = x_low + 1;     \
+    T ly = y - y_low, lx = x - x_low, hy = 1. - ly, hx = 1. - lx;                                      \
+    T v1 = in[y_low * width + x_low], v2 = in[y_low * width + x_high];                                 \
+    T v3 = in[y_high * width + x_low], v4 = in[y_high * width + x_high];                               \
+    T w1 = hy * hx, w2 = hy * lx, w3 = ly * hx, w4 = ly * lx;                                          \
+    return (w1 * v1 + w2 * v2 + w3 * v3 + w4 * v4);                                                    \
+  }                                                                                                    \
+  API void oracle_ps_roi_align_forward_##SFX(const T* input, const T* rois, T* output, int* mapping,   \
+                                             int num_rois, int channels, int height, int width,        \
+                                             int ph_n, int pw_n, double scale_d, int sampling_ratio) { \
+    const T spatial_scale = (T)scale_d;                                                                \
+    const int channels_out = channels / (ph_n * pw_n);                                                 \
+    for (int n = 0; n < num_rois; ++n) {                                                               \
+      const T* r = rois + n * 5;                                                                       \
+      int b = (int)r[0];                                                                               \
+      T sw = r[1] * spatial_scale - (T)0.5, sh = r[2] * spatial_scale - (T)0.5;                        \
+      T ew = r[3] * spatial_scale - (T)0.5, eh = r[4] * spatial_scale - (T)0.5;                        \
+      T roi_w = ew - sw, roi_h = eh - sh;                                                              \
+      T bin_h = roi_h / (T)ph_n, bin_w = roi_w / (T)pw_n;                                              \
+      int c_in = 0;                                                                                    \
+      for (int c_out = 0; c_out < channels_out; ++c_out)                                               \
+        for (int ph = 0; ph < ph_n; ++ph)                                                              \
+          for (int pw = 0; pw < pw_n; ++pw) {                                                          \
+            long o = (((long)n * channels_out + c_out) * ph_n + ph) * pw_n + pw;                       \
+            T hstart = (T)ph * bin_h + sh, wstart = (T)pw * bin_w + sw;                                \
+            int gh = sampling_ratio > 0 ? sampling_ratio : (int)ceil(roi_h / ph_n);                    \
+            int gw = sampling_ratio > 0 ? sampling_ratio : (int)ceil(roi_w / pw_n);                    \
+            const T count = gh * gw;                                                                   \
+            const T* in = input + ((long)b * channels + c_in) * height * width;                        \
+            T sum = 0;                                                                                 \
+            for (int iy = 0; iy < gh; iy++) {                                                          \
+              const T y = hstart + (T)(iy + .5f) * bin_h / (T)gh;                                      \
+              for (int ix = 0; ix < gw; ix++) {                                                        \
+                const T x = wstart + (T)(ix + .5f) * bin_w / (T)gw;                                    \
+                sum += ps_bilinear_##SFX(in, height, width, y, x);                                     \
+              }                                                                                        \
+            }                                                                                          \
+            sum /= count;                                                                              \
+            output[o] = sum;                                                                           \
+            mapping[o] = c_in;                                                                         \
+            c_in++;                                                                                    \
+          }                                                                                            \
+    }                                                                                                  \
+  }                                                                                                    \
+  API void oracle_ps_roi_align_backward_##SFX(const T* grad, const int* mapping, const T* rois,        \
+                                              T* grad_input, int num_rois, int channels, int height,   \
+                                              int width, int ph_n, int pw_n, double scale_d,           \
+                                              int sampling_ratio) {                                    \
+    const T spatial_scale = (T)scale_d;                                                                \
+    const int channels_out = channels / (ph_n * pw_n);                                                 \
+    const long nthreads = (long)num_rois * channels_out * ph_n * pw_n;                                 \
+    for (long index = 0; index < nthreads; index++) {                                                  \
+      int pw = index % pw_n, ph = (index / pw_n) % ph_n;                                               \
+      long n = index / pw_n / ph_n / channels_out;                                                     \
+      const T* r = rois + n * 5;                                                                       \
+      int b = (int)r[0];                                                                               \
+      T sw = r[1] * spatial_scale - (T)0.5, sh = r[2] * spatial_scale - (T)0.5;                        \
+      T ew = r[3] * spatial_scale - (T)0.5, eh = r[4] * spatial_scale - (T)0.5;                        \
+      T roi_w = ew - sw, roi_h = eh - sh;                                                              \
+      T bin_h = roi_h / (T)ph_n, bin_w = roi_w / (T)pw_n;                                              \
+      int c_in = mapping[index];                                                                       \
+      T* gi = grad_input + ((long)b * channels + c_in) * height * width;                               \
+      T hstart = (T)ph * bin_h + sh, wstart = (T)pw * bin_w + sw;                                      \
+      const T go = grad[index];                                                                        \
+      int gh = sampling_ratio > 0 ? sampling_ratio : (int)ceil(roi_h / ph_n);                          \
+      int gw = sampling_ratio > 0 ? sampling_ratio : (int)ceil(roi_w / pw_n);                          \
+      const T count = gh * gw;                                                                         \
+      for (int iy = 0; iy < gh; iy++) {                                                                \
+        T y = hstart + (T)(iy + .5f) * bin_h / (T)gh;                                                  \
+        for (int ix = 0; ix < gw; ix++) {                                                              \
+          T x = wstart + (T)(ix + .5f) * bin_w / (T)gw;                                                \
+          T yy = y, xx = x;                                                                            \
+          if (yy < -1.0 || yy > height || xx < -1.0 || xx > width) continue;                           \
+          if (yy <= 0) yy = 0;                                                                         \
+          if (xx <= 0) xx = 0;                                                                         \
+          int y_low = (int)yy, x_low = (int)xx, y_high, x_high;                                        \
+          if (y_low >= height - 1) { y_high = y_low = height - 1; yy = (T)y_low; } else y_high = y_low + 1; \
+          if (x_low >= width - 1) { x_high = x_low = width - 1; xx = (T)x_low; } else x_high = x_low + 1;   \
+          T ly = yy - y_low, lx = xx - x_low, hy = 1. - ly, hx = 1. - lx;                              \
+          T w1 = hy * hx, w2 = hy * lx, w3 = ly * hx, w4 = ly * lx;                                    \
+          gi[y_low * width + x_low] += go * w1 / count;                                                \
+          gi[y_low * width + x_high] += go * w2 / count;                                               \
+          gi[y_high * width + x_low] += go * w3 / count;                                               \
+          gi[y_high * width + x_high] += go * w4 / count;                                              \
+        }                                                                                              \
+      }                                                                                                \
+    }                                                                                                  \
+  }
+
+ORACLE_PS_ROI_ALIGN(float, f32)
+ORACLE_PS_ROI_ALIGN(double, f64)

@@ -49,6 +49,18 @@ for (ph, pw, cmul) in ((3, 3, 2), (2, 4, 3), (1, 1, 5)):
         pcases.append(dict(ph=ph, pw=pw, scale=scale, x=xp, out=y.detach().clone(), grad_out=gy, grad_in=xi.grad.clone()))
 torch.save(dict(rois=rois, cases=pcases), "%(out)s/ps_roi_pool.pt")
 print("ps_roi_pool golden written", len(pcases))
+acases = []
+for (ph, pw, cmul) in ((3, 3, 2), (2, 4, 3)):
+    xp = torch.randn(2, cmul * ph * pw, 23, 31, generator=g)
+    for (scale, sr) in ((0.25, 2), (1.0 / 3.0, -1), (0.25, 3)):
+        xi = xp.clone().requires_grad_(True)
+        y = ops.ps_roi_align(xi, rois, (ph, pw), scale, sr)
+        gy = torch.randn(y.shape, generator=g)
+        y.backward(gy)
+        acases.append(dict(ph=ph, pw=pw, scale=scale, sr=sr, x=xp, out=y.detach().clone(), grad_out=gy,
+                           grad_in=xi.grad.clone()))
+torch.save(dict(rois=rois, cases=acases), "%(out)s/ps_roi_align.pt")
+print("ps_roi_align golden written", len(acases))
 '''
 
 

@@ -200,3 +200,34 @@ def test_ps_roi_pool_restatement_matches_compiled_reference(dtype):
             go = torch.randn(a.shape, generator=g, dtype=dtype)
             assert torch.equal(oracle.ps_roi_pool_backward(go, rois, ma, scale, ph, pw, *x.shape, impl="oracle"),
                                oracle.ps_roi_pool_backward(go, rois, mb, scale, ph, pw, *x.shape, impl="ref"))
+
+
+def test_ps_roi_align_golden(golden):
+    d = golden("ps_roi_align.pt")
+    for c in d["cases"]:
+        out, cm = oracle.ps_roi_align_forward(c["x"], d["rois"], c["ph"], c["pw"], c["scale"], c["sr"])
+        # adaptive grids of malformed RoIs are empty: 0 / 0 = NaN in the reference and here
+        assert torch.equal(out.isnan(), c["out"].isnan()), (c["ph"], c["scale"], c["sr"])
+        assert torch.equal(out.nan_to_num(), c["out"].nan_to_num()), (c["ph"], c["scale"], c["sr"])
+        gi = oracle.ps_roi_align_backward(c["grad_out"], d["rois"], cm, c["scale"], c["ph"], c["pw"], c["sr"],
+                                          *c["x"].shape)
+        assert torch.equal(gi.nan_to_num(), c["grad_in"].nan_to_num())
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/libtvref.so not built")
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_ps_roi_align_restatement_matches_compiled_reference(dtype):
+    g = torch.Generator().manual_seed(17)
+    K = 50
+    rois = torch.rand(K, 5, generator=g, dtype=dtype) * 30 - 3
+    rois[:, 0] = torch.randint(0, 3, (K,), generator=g).to(dtype)
+    rois[:, 3:] = rois[:, 1:3] + torch.rand(K, 2, generator=g, dtype=dtype) * 25 + 0.5
+    for ph, pw, cm_ in ((2, 3, 2), (1, 1, 4), (3, 3, 1)):
+        x = torch.randn(3, cm_ * ph * pw, 17, 23, generator=g, dtype=dtype)
+        for scale, sr in ((1.0, 2), (0.5, -1), (0.3, 1)):
+            a, ma = oracle.ps_roi_align_forward(x, rois, ph, pw, scale, sr, impl="oracle")
+            b, mb = oracle.ps_roi_align_forward(x, rois, ph, pw, scale, sr, impl="ref")
+            assert torch.equal(a, b) and torch.equal(ma, mb), (scale, sr, ph, pw)
+            go = torch.randn(a.shape, generator=g, dtype=dtype)
+            assert torch.equal(oracle.ps_roi_align_backward(go, rois, ma, scale, ph, pw, sr, *x.shape, impl="oracle"),
+                               oracle.ps_roi_align_backward(go, rois, mb, scale, ph, pw, sr, *x.shape, impl="ref"))
