@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(kTile) nms_seg_mask_kernel(const int32_t* __re
 // nms_scan_kernel (any N): rows of kept boxes are read from global memory.
 constexpr int kScanThreads = 1024;
 constexpr int kSmemThreads = 512;
-constexpr int kSmemBlocks = 208;  // 1040 bytes of shared memory per block: 211 KB
+constexpr int kSmemBlocks = 208;  // 1040 bytes of shared memory per block + 2 KB of diagonal ring: 213 KB
 
 __device__ __forceinline__ u64 resolve_block(u64 alive, const u64* __restrict__ diag, int stride) {
   u64 d[kTile];
@@ -282,72 +282,176 @@ __device__ __forceinline__ void compact_keep(const u64* keptw, int col_blocks, c
   if (tid == 0) *num_keep = (top_n > 0 && running > top_n) ? top_n : running;
 }
 
+// Pipelined: warp 0 is the serial resolver and runs one block AHEAD of the other warps.  In iteration b it
+// completes remv[b + 1] with the kept rows of block b (only that one word) and resolves block b + 1 from its
+// prefetched diagonal words, while warps 1.. OR the kept rows of block b into the words to the right of
+// b + 1: one barrier per block, the dependent resolve overlaps the OR phase.
+//   * the 64 rows of a block are contiguous in the mask, so ONE bulk copy (cp.async.bulk + mbarrier) stages
+//     them; per-thread 8-byte cp.async made the LSU the bottleneck (1500 cycles per block).
+//   * a block is resolved as a fixed point by the whole warp instead of a 64-step dependent chain:
+//     K <- alive & ~OR{row j : j in K}, rows restricted to bits > j.  Bits below t are final after t rounds
+//     (strictly upper-triangular dependence), so K' == K is reached in <= 64 rounds and is the greedy
+//     result; typical boxes need a handful (the longest suppression chain inside the block).
+constexpr int kDiagRing = 4;
+#ifdef B200DET_SCAN_PROFILE
+__device__ long long g_scan_prof[10];
+#define SCAN_T(k) { const long long t_ = clock64(); prof_[k] += t_ - t0_; t0_ = t_; }
+#else
+#define SCAN_T(k)
+#endif
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_wait(u64* bar, unsigned parity) {
+  unsigned ok;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!ok);
+}
+
+// greedy keep bits of one 64-box block; lane l holds diagonal rows l and l + 32.  Whole warp, uniform result.
+__device__ __forceinline__ u64 resolve_block_warp(u64 alive, u64 d0, u64 d1, int lane) {
+  d0 &= ~((2ULL << lane) - 1ULL);         // bits > lane
+  d1 &= ~((2ULL << (lane + 32)) - 1ULL);  // bits > lane + 32 (none for row 63)
+  u64 K = alive;
+  for (;;) {
+    u64 v = ((K >> lane) & 1ULL) ? d0 : 0ULL;
+    v |= ((K >> (lane + 32)) & 1ULL) ? d1 : 0ULL;
+    const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v);
+    const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
+    const u64 Kn = alive & ~(((u64)hi << 32) | (u64)lo);
+    if (Kn == K) return K;
+    K = Kn;
+  }
+}
+
+// OR phase of one block for the kSmemThreads - 32 worker threads: group q takes rows [q * RPG, (q + 1) * RPG),
+// unrolled so the loads of the kept rows are independent and pipelined
+template <int RPG>
+__device__ __forceinline__ void or_rows(const u64* __restrict__ rowsb, u64* remv, u64 kept, int j0, int col_blocks,
+                                        int t) {
+  constexpr int kGroups = kTile / RPG, kPer = (kSmemThreads - 32) / kGroups;
+  const int q = t / kPer;
+  const unsigned kq = (unsigned)(kept >> (q * RPG)) & (RPG == 32 ? 0xffffffffu : ((1u << RPG) - 1u));
+  if (!kq) return;
+  for (int j = j0 + (t - q * kPer); j < col_blocks; j += kPer) {
+    const u64* col = rowsb + (size_t)(q * RPG) * col_blocks + j;
+    u64 acc = 0;
+#pragma unroll
+    for (int i = 0; i < RPG; ++i) {
+      if ((kq >> i) & 1u) acc |= col[(size_t)i * col_blocks];  // predicated loads: dropped rows cost no bandwidth
+    }
+    // two 32-bit shared atomics: a 64-bit OR on shared memory is a CAS loop, and the groups meet here
+    unsigned* w = reinterpret_cast<unsigned*>(remv + j);
+    if ((unsigned)acc) atomicOr(w, (unsigned)acc);
+    if ((unsigned)(acc >> 32)) atomicOr(w + 1, (unsigned)(acc >> 32));
+  }
+}
+
 __device__ __forceinline__ void scan_smem_body(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
     int64_t* __restrict__ keep, int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n) {
-  extern __shared__ u64 smem[];
-  u64* remv = smem;                     // [col_blocks]
-  u64* keptw = smem + col_blocks;       // [col_blocks]
-  u64* stage = smem + 2 * col_blocks;   // [2][kTile * col_blocks]
+  extern __shared__ __align__(16) u64 smem[];
+  u64* remv = smem;                                    // [col_blocks]
+  u64* keptw = smem + col_blocks;                      // [col_blocks]
+  u64* ring = smem + 2 * col_blocks;                   // [kDiagRing][kTile] diagonal words
+  u64* stage = ring + kDiagRing * kTile;               // [2][kTile * col_blocks], 16-byte aligned
+  __shared__ __align__(8) u64 s_bar[2];
   __shared__ u64 s_kept;
   __shared__ int s_base[32];
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int j = tid; j < col_blocks; j += kSmemThreads) remv[j] = init_remv ? init_remv[j] : 0ULL;
-
-  auto prefetch = [&](int b) {  // words j >= b of the rows of block b; a warp copies whole rows
-    u64* dst = stage + (size_t)(b & 1) * kTile * col_blocks;
-    const int rows = min(n - b * kTile, kTile);
-    const int warp = tid >> 5, lane = tid & 31;
-    for (int i = warp; i < rows; i += kSmemThreads / 32) {
-      const u64* src = mask + (size_t)(b * kTile + i) * col_blocks;
-      u64* d = dst + i * col_blocks;
-      for (int j = b + lane; j < col_blocks; j += 32) {
-        const unsigned sa = (unsigned)__cvta_generic_to_shared(d + j);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(src + j) : "memory");
-      }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  };
-  prefetch(0);
-  for (int b = 0; b < col_blocks; ++b) {
-    if (b + 1 < col_blocks) {
-      prefetch(b + 1);
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-    } else {
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-    }
-    __syncthreads();
-    const u64* rowsb = stage + (size_t)(b & 1) * kTile * col_blocks;
-    const int rows = min(n - b * kTile, kTile);
-    if (tid == 0) {
-      u64 alive = ~remv[b];
-      if (rows < kTile) alive &= (1ULL << rows) - 1ULL;
-      // rows >= `rows` of the stage hold stale data, but their alive bits are clear
-      const u64 kept = resolve_block(alive, rowsb + b, col_blocks);
-      s_kept = kept;
-      keptw[b] = kept;
-    }
-    __syncthreads();
-    // OR the kept rows into the words to the right: 4 thread groups take 16 rows each, branch-free
-    const u64 kept = s_kept;
-    {
-      constexpr int kPer = kSmemThreads / 4;
-      const int q = tid / kPer;
-      const unsigned kq = (unsigned)(kept >> (16 * q)) & 0xffffu;
-      if (kq)
-        for (int j = b + 1 + (tid - q * kPer); j < col_blocks; j += kPer) {
-          const u64* col = rowsb + (size_t)(16 * q) * col_blocks + j;
-          u64 acc = 0;
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const u64 v = col[(size_t)i * col_blocks];
-            acc |= ((kq >> i) & 1u) ? v : 0ULL;
-          }
-          if (acc) atomicOr(remv + j, acc);
-        }
-    }
-    __syncthreads();  // stage (b & 1) is refilled by the prefetch of block b + 2
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[0])) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[1])) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  __syncthreads();
+
+  // rows of block b (all 64 are real for every block but the last, whose rows nobody reads): contiguous in the
+  // mask, so one bulk copy.  The words left of the diagonal ride along: a bulk copy per row for only the right
+  // part was measured at ~60 cycles of issue per copy (3900 cycles per block), far worse than the extra bytes.
+  auto prefetch_rows = [&](int b) {  // one thread
+    if (b + 1 >= col_blocks) return;
+    const unsigned bytes = (unsigned)(kTile * col_blocks * sizeof(u64));
+    const unsigned bar = smem_u32(&s_bar[b & 1]);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic reads of this stage are done
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(stage + (size_t)(b & 1) * kTile * col_blocks)),
+                   "l"(mask + (size_t)b * kTile * col_blocks), "r"(bytes), "r"(bar) : "memory");
+  };
+  auto prefetch_diag = [&](int b, int i) {  // mask[b*64 + i][b], i < rows
+    if (b >= col_blocks || i >= min(n - b * kTile, kTile)) return;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;"
+                 ::"r"(smem_u32(ring + (b & (kDiagRing - 1)) * kTile + i)),
+                   "l"(mask + (size_t)(b * kTile + i) * col_blocks + b) : "memory");
+  };
+  auto resolve = [&](int b, u64 removed) {  // warp 0, all lanes
+    const int rows = min(n - b * kTile, kTile);
+    u64 alive = ~removed;
+    if (rows < kTile) alive &= (1ULL << rows) - 1ULL;  // stale ring entries belong to cleared bits
+    const u64* d = ring + (b & (kDiagRing - 1)) * kTile;
+    return resolve_block_warp(alive, d[lane], d[lane + 32], lane);
+  };
+
+  if (tid == 32) prefetch_rows(0);
+  if (tid >= 64 && tid < 64 + kTile) {
+    prefetch_diag(0, tid - 64);
+    prefetch_diag(1, tid - 64);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) {
+    const u64 k0 = resolve(0, remv[0]);
+    if (lane == 0) keptw[0] = k0;
+  }
+#ifdef B200DET_SCAN_PROFILE
+  long long prof_[5] = {0, 0, 0, 0, 0};
+  long long t0_ = clock64();
+#endif
+  for (int b = 0; b < col_blocks; ++b) {
+    if (b + 1 < col_blocks) mbar_wait(&s_bar[b & 1], (unsigned)(b >> 1) & 1u);  // rows(b) landed
+    asm volatile("cp.async.wait_group 0;" ::: "memory");                        // this thread's diag(b+1) words
+    SCAN_T(0)
+    __syncthreads();  // OR phase of block b-1 done; keptw[b] and diag(b+1) visible
+    SCAN_T(1)
+    if (tid == 32) prefetch_rows(b + 1);  // into the stage block b-1 has left
+    if (tid >= 64 && tid < 64 + kTile) prefetch_diag(b + 2, tid - 64);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    SCAN_T(2)
+    const u64 kept = keptw[b];
+    const u64* rowsb = stage + (size_t)(b & 1) * kTile * col_blocks;
+    if (warp == 0) {
+      if (b + 1 < col_blocks) {
+        // word b+1 of the kept rows of block b: two rows per lane, OR across the warp
+        u64 v = 0;
+        if ((kept >> lane) & 1ULL) v |= rowsb[(size_t)lane * col_blocks + b + 1];
+        if ((kept >> (lane + 32)) & 1ULL) v |= rowsb[(size_t)(lane + 32) * col_blocks + b + 1];
+        const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v);
+        const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
+        SCAN_T(3)
+        const u64 k1 = resolve(b + 1, remv[b + 1] | ((u64)hi << 32) | (u64)lo);
+        if (lane == 0) keptw[b + 1] = k1;
+        SCAN_T(4)
+      }
+    } else if (kept && b + 2 < col_blocks) {
+      // OR the kept rows into the words right of b+1: G thread groups take 64 / G rows each, a thread strides
+      // over the words; more groups as fewer words remain
+      const int ncols = col_blocks - (b + 2), t = tid - 32;
+      if (ncols > 120) or_rows<32>(rowsb, remv, kept, b + 2, col_blocks, t);
+      else if (ncols > 60) or_rows<16>(rowsb, remv, kept, b + 2, col_blocks, t);
+      else if (ncols > 30) or_rows<8>(rowsb, remv, kept, b + 2, col_blocks, t);
+      else or_rows<4>(rowsb, remv, kept, b + 2, col_blocks, t);
+    }
+    if (warp != 0) { SCAN_T(3) }
+  }
+#ifdef B200DET_SCAN_PROFILE
+  if (tid == 0 || tid == 40)
+    for (int k = 0; k < 5; ++k) g_scan_prof[k + (tid ? 5 : 0)] = prof_[k];
+#endif
+  __syncthreads();
   compact_keep(keptw, col_blocks, order, keep, num_keep, s_base, &s_kept, top_n);
 }
 
@@ -504,7 +608,7 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
   nms_mask_kernel<BoxT><<<grid, kTile, 0, st>>>((int)n, (float)thr, (const BoxT*)L.sorted,
                                                mode == 2 ? L.cls : nullptr, L.mask);
   if (col_blocks <= kSmemBlocks) {
-    const size_t smem = ((size_t)2 * col_blocks + (size_t)2 * kTile * col_blocks) * sizeof(u64);
+    const size_t smem = ((size_t)2 * col_blocks + kDiagRing * kTile + (size_t)2 * kTile * col_blocks) * sizeof(u64);
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     nms_scan_smem_kernel<<<1, kSmemThreads, smem, st>>>(L.mask, (int)n, col_blocks, L.order, keep, num_keep);
@@ -685,7 +789,7 @@ bool seg_shape(const int64_t* seg_offsets, long long S, long long N, long long* 
     const long long n = seg_offsets[s + 1] - seg_offsets[s];
     if (n < 0) return false;
     const long long cb = (n + kTile - 1) / kTile;
-    *mask_words += n * cb;
+    *mask_words += (n * cb + 1) & ~1LL;
     *remv_words += cb;
     if (cb > *cb_max) *cb_max = (int)cb;
   }
@@ -717,7 +821,7 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
         // mode < 0: the reference's rule for a CUDA tensor, image by image (boxes.py:72)
         b.mode[j] = (signed char)(!idxs ? 0 : (mode >= 0 ? mode : (4 * ns > 20000 ? 2 : 1)));
         const long long cb = (ns + kTile - 1) / kTile;
-        mo += ns * cb;
+        mo += (ns * cb + 1) & ~1LL;  // 16-byte aligned segments: the scan stages rows with bulk copies
         ro += (int)cb;
       }
     }
@@ -739,7 +843,7 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
     nms_seg_mask_kernel<Box4f><<<grid, kTile, 0, st>>>(L.off, L.moff, L.smode, (float)thr, L.sorted, L.cls, L.mask);
   }
   if (cb_max <= kSmemBlocks) {
-    const size_t smem = ((size_t)2 * cb_max + (size_t)2 * kTile * cb_max) * sizeof(u64) + 16;
+    const size_t smem = ((size_t)2 * cb_max + kDiagRing * kTile + (size_t)2 * kTile * cb_max) * sizeof(u64) + 16;
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_seg_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     nms_seg_scan_smem_kernel<<<(unsigned)S, kSmemThreads, smem, st>>>(L.mask, L.off, L.moff, L.roff, L.order, keep,
