@@ -17,6 +17,7 @@
 // IoU follows devIoU (cuda/nms_kernel.cu:16-29) with every operation an
 // explicit round-to-nearest intrinsic so no FMA contraction can change a
 // comparison: inter / ((Sa + Sb) - inter) > (float)threshold.
+#include <type_traits>
 #include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
@@ -151,6 +152,52 @@ __device__ __forceinline__ bool boxes_meet<Box4d>(const Box4d& a, const Box4d& b
   return fmin(a.x2, b.x2) > fmax(a.x1, b.x1) && fmin(a.y2, b.y2) > fmax(a.y1, b.y1);
 }
 
+// fp32 fast path.  The reference decides fl(inter / union) > thr (nms_kernel.cu's devIoU); an IEEE division per
+// pair is ~12 instructions plus a slow-path branch.  r = fma(-thr, union, inter) has the sign of
+// inter / union - thr with ONE rounding, so whenever |r| > 2^-21 * union (and union > 0) the quotient is more
+// than 4 ulp(thr) away from thr and its rounding cannot change the answer: such pairs are decided by the sign
+// of r.  The rest (a few per million; also union <= 0, NaN, inf, where the comparisons come out false) are
+// collected in a second bit word and decided by the exact division afterwards.  Valid for 2^-20 <= thr <= 1.
+constexpr float kSureMargin = 4.76837158203125e-07f;  // 2^-21
+
+__device__ __forceinline__ float box_area(const Box4f& b) {
+  return __fmul_rn(__fsub_rn(b.x2, b.x1), __fsub_rn(b.y2, b.y1));
+}
+
+template <bool HAS_CLS>
+__device__ __forceinline__ u64 tile_bits_f32(const Box4f& a, float sa, int32_t ac, const Box4f* __restrict__ cb,
+                                             const float* __restrict__ carea, const int32_t* __restrict__ cc,
+                                             float thr, u64 valid) {
+  unsigned w[2] = {0u, 0u}, u[2] = {0u, 0u};
+#pragma unroll
+  for (int i = 0; i < kTile; ++i) {
+    const Box4f b = cb[i];
+    const float left = fmaxf(a.x1, b.x1), right = fminf(a.x2, b.x2);
+    const float top = fmaxf(a.y1, b.y1), bottom = fminf(a.y2, b.y2);
+    const float iw = fmaxf(__fsub_rn(right, left), 0.f), ih = fmaxf(__fsub_rn(bottom, top), 0.f);
+    const float inter = __fmul_rn(iw, ih);
+    const float uni = __fsub_rn(__fadd_rn(sa, carea[i]), inter);
+    const float r = __fmaf_rn(-thr, uni, inter);
+    bool sure = (uni > 0.f) && (fabsf(r) > __fmul_rn(uni, kSureMargin));
+    bool hit = sure && (r > 0.f);
+    if (HAS_CLS) {
+      const bool same = cc[i] == ac;
+      hit = hit && same;
+      sure = sure || !same;
+    }
+    if (hit) w[i >> 5] |= 1u << (i & 31);
+    if (!sure) u[i >> 5] |= 1u << (i & 31);
+  }
+  u64 bits = (((u64)w[1] << 32) | w[0]) & valid;
+  u64 open = (((u64)u[1] << 32) | u[0]) & valid;
+  while (open) {  // rare: the exact quotient decides
+    const int i = __ffsll((long long)open) - 1;
+    open &= open - 1;
+    if (iou_gt(a, cb[i], thr)) bits |= 1ULL << i;
+  }
+  return bits;
+}
+
 template <typename BoxT>
 __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restrict__ boxes,
                                            const int32_t* __restrict__ cls, u64* __restrict__ mask,
@@ -159,11 +206,16 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
   const int row_size = min(n - row_start * kTile, kTile);
   __shared__ BoxT cb[kTile];
   __shared__ int32_t cc[kTile];
+  __shared__ float carea[kTile];
   const int cur = kTile * row_start + threadIdx.x;
   const bool have_row = (int)threadIdx.x < row_size;
   BoxT a = boxes[have_row ? cur : kTile * row_start];
   const int32_t ac = (cls && have_row) ? cls[cur] : 0;
   const bool skip_apart = thr >= 0.f;
+  constexpr bool kF32 = std::is_same<BoxT, Box4f>::value;
+  const bool fast = kF32 && thr >= 9.5367431640625e-07f && thr <= 1.f;
+  float sa = 0.f;
+  if constexpr (kF32) sa = box_area(a);
   for (int t = 0; t < kColTiles; ++t) {
     const int col_start = col_group * kColTiles + t;
     if (col_start >= col_blocks) break;
@@ -171,20 +223,32 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
     const int col_size = min(n - col_start * kTile, kTile);
     __syncthreads();  // the previous tile's columns are no longer read
     if ((int)threadIdx.x < col_size) {
-      cb[threadIdx.x] = boxes[kTile * col_start + threadIdx.x];
+      const BoxT b = boxes[kTile * col_start + threadIdx.x];
+      cb[threadIdx.x] = b;
       cc[threadIdx.x] = cls ? cls[kTile * col_start + threadIdx.x] : 0;
+      if constexpr (kF32) carea[threadIdx.x] = box_area(b);
     }
     __syncthreads();
-    if (have_row) {
-      u64 w = 0;
-      const int start = (row_start == col_start) ? threadIdx.x + 1 : 0;
-      for (int i = start; i < col_size; ++i) {
-        if (cc[i] != ac) continue;
-        if (skip_apart && !boxes_meet(a, cb[i])) continue;
-        if (iou_gt(a, cb[i], thr)) w |= 1ULL << i;
+    if (!have_row) continue;
+    const int start = (row_start == col_start) ? threadIdx.x + 1 : 0;
+    u64 w = 0;
+    if constexpr (kF32) {
+      if (fast) {
+        // entries past col_size hold stale boxes; their bits are masked off, like those up to the diagonal
+        u64 valid = col_size == kTile ? ~0ULL : ((1ULL << col_size) - 1ULL);
+        valid &= start >= kTile ? 0ULL : (~0ULL << start);
+        w = cls ? tile_bits_f32<true>(a, sa, ac, cb, carea, cc, thr, valid)
+                : tile_bits_f32<false>(a, sa, ac, cb, carea, cc, thr, valid);
+        mask[(long long)cur * col_blocks + col_start] = w;
+        continue;
       }
-      mask[(long long)cur * col_blocks + col_start] = w;
     }
+    for (int i = start; i < col_size; ++i) {
+      if (cc[i] != ac) continue;
+      if (skip_apart && !boxes_meet(a, cb[i])) continue;
+      if (iou_gt(a, cb[i], thr)) w |= 1ULL << i;
+    }
+    mask[(long long)cur * col_blocks + col_start] = w;
   }
 }
 
