@@ -267,3 +267,44 @@ def test_segmented_equals_loop_of_batched_nms_full_size(capi):
         ref = capi.batched_nms(bd[sl], sd[sl], ld[sl], 0.7)[:1000] + off[k]
         assert torch.equal(got[k], ref)
         assert torch.equal(got[k].cpu(), _segmented_oracle(b, s, lvl, off, 0.7, None, "auto", 1000)[k]) if k == 0 else True
+
+
+def test_iou_on_the_threshold_and_degenerate_boxes(capi):
+    """The fp32 mask decides most pairs by the sign of fma(-thr, union, inter) and falls back to the exact
+    quotient near the threshold: pairs whose IoU IS the threshold (integer grids: 1/2, 1/3, 1/4 ...), pairs one
+    ulp either side of it, inverted / zero-area / huge boxes must all come out as the reference's division does."""
+    g = torch.Generator().manual_seed(77)
+    n = 1500
+    xy = torch.randint(0, 12, (n, 2), generator=g).float()
+    wh = torch.randint(1, 5, (n, 2), generator=g).float()
+    grid = torch.cat([xy, xy + wh], 1)                       # small integer boxes: many exact rational IoUs
+    s = torch.randperm(n, generator=g).float()
+    for thr in (0.5, 1.0 / 3.0, 0.25, 0.2, 2.0 / 3.0, 0.75, 1.0, 1e-6, 0.0, -1.0, 1.5):
+        assert torch.equal(capi.nms(grid.to(DEV), s.to(DEV), thr).cpu(), oracle.nms(grid, s, thr)), thr
+    # one ulp around: widen one side of a duplicate so that IoU = w / (w + d) sweeps through 0.5
+    base = torch.tensor([0.0, 0.0, 1.0, 1.0])
+    rows, x = [base], torch.tensor(2.0)
+    for _ in range(40):
+        x = torch.nextafter(x, torch.tensor(0.0))
+        rows.append(torch.stack([base[0], base[1], x, base[3]]))
+    x = torch.tensor(2.0)
+    for _ in range(40):
+        x = torch.nextafter(x, torch.tensor(4.0))
+        rows.append(torch.stack([base[0], base[1], x, base[3]]))
+    near = torch.stack(rows)
+    sn = torch.arange(len(rows), 0, -1).float()
+    for thr in (0.5, float(torch.nextafter(torch.tensor(0.5), torch.tensor(1.0))),
+                float(torch.nextafter(torch.tensor(0.5), torch.tensor(0.0)))):
+        assert torch.equal(capi.nms(near.to(DEV), sn.to(DEV), thr).cpu(), oracle.nms(near, sn, thr)), thr
+    # inverted (negative area), zero-area, huge and tiny boxes mixed into a normal set
+    b, s2 = make_boxes(g, 600, span=60.0)
+    b[::7, 2:] = b[::7, :2] - 3.0                            # x2 < x1, y2 < y1
+    b[3::11, 2:] = b[3::11, :2]                              # zero area
+    b[5::13] *= 1e18                                         # areas overflow to inf
+    b[6::17] *= 1e-22                                        # areas underflow
+    for thr in (0.3, 0.5):
+        assert torch.equal(capi.nms(b.to(DEV), s2.to(DEV), thr).cpu(), oracle.nms(b, s2, thr)), thr
+    idx = torch.randint(0, 4, (600,), generator=g)
+    for mode, name in ((capi.BNMS_TRICK, "trick"), (capi.BNMS_VANILLA, "vanilla")):
+        got = capi.batched_nms(grid[:600].to(DEV), s[:600].to(DEV), idx.to(DEV), 0.5, mode)
+        assert torch.equal(got.cpu(), oracle.batched_nms(grid[:600], s[:600], idx, 0.5, name)), name
