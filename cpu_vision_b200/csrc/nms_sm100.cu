@@ -18,6 +18,7 @@
 // explicit round-to-nearest intrinsic so no FMA contraction can change a
 // comparison: inter / ((Sa + Sb) - inter) > (float)threshold.
 #include <type_traits>
+#include <cub/block/block_radix_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
@@ -132,6 +133,77 @@ __global__ void nms_gather_kernel(const T* __restrict__ boxes, const int64_t* __
   b.x1 = x1; b.y1 = y1; b.x2 = x2; b.y2 = y2;
   sorted[i] = b;
   if (sorted_cls) sorted_cls[i] = (int32_t)idxs[src];
+}
+
+// ---- 1-3 fused for detection-sized sets ----------------------------------------
+// Up to kSortMax boxes: ONE CTA builds the keys, sorts them (block radix sort: LSD, stable, the same
+// float ordering as the device-wide sort), reduces the maximum coordinate and gathers the boxes.  The
+// device-wide radix sort costs 6 launches of 3-11 us for 5000 keys and prepare / max / gather three more;
+// this is one launch.  Padding keys sort last (0xffffffff is the lowest float in radix order; a real key
+// with that bit pattern still precedes the padding because the sort is stable).
+constexpr int kSortThreads = 1024, kSortItems = 8, kSortMax = kSortThreads * kSortItems;
+
+template <typename T>
+__global__ void __launch_bounds__(kSortThreads) nms_front_small_kernel(
+    const T* __restrict__ boxes, const T* __restrict__ scores, const int64_t* __restrict__ idxs, int n, int mode,
+    Box4f* __restrict__ sorted, int32_t* __restrict__ sorted_cls, int32_t* __restrict__ order) {
+  using Sort = cub::BlockRadixSort<float, kSortThreads, kSortItems, int32_t>;
+  __shared__ typename Sort::TempStorage tmp;
+  __shared__ float red[32];
+  __shared__ float s_max;
+  const int tid = threadIdx.x;
+  float k[kSortItems];
+  int32_t v[kSortItems];
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j) {
+    const int i = tid * kSortItems + j;
+    k[j] = i < n ? (float)Io<T>::ld(scores + i) : __int_as_float(-1);
+    v[j] = i < n ? i : 0x7fffffff;
+  }
+  Sort(tmp).SortDescending(k, v);
+  if (mode == 1) {  // boxes.max() as nms_max_coord_kernel computes it (NaN propagates)
+    float m = -INFINITY;
+    bool nan = false;
+    for (int i = tid; i < 4 * n; i += kSortThreads) {
+      const float x = Io<T>::ld(boxes + i);
+      nan |= (x != x);
+      m = x > m ? x : m;
+    }
+    if (nan) m = NAN;
+    for (int o = 16; o > 0; o >>= 1) {
+      const float other = __shfl_xor_sync(0xffffffffu, m, o);
+      m = (other != other || m != m) ? NAN : (other > m ? other : m);
+    }
+    if ((tid & 31) == 0) red[tid >> 5] = m;
+    __syncthreads();
+    if (tid < 32) {
+      m = red[tid];
+      for (int o = 16; o > 0; o >>= 1) {
+        const float other = __shfl_xor_sync(0xffffffffu, m, o);
+        m = (other != other || m != m) ? NAN : (other > m ? other : m);
+      }
+      if (tid == 0) s_max = m;
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j) {
+    const int p = tid * kSortItems + j;
+    if (p >= n) continue;
+    const int src = v[j];
+    order[p] = src;
+    float x1 = Io<T>::ld(boxes + (size_t)src * 4 + 0), y1 = Io<T>::ld(boxes + (size_t)src * 4 + 1);
+    float x2 = Io<T>::ld(boxes + (size_t)src * 4 + 2), y2 = Io<T>::ld(boxes + (size_t)src * 4 + 3);
+    if (mode == 1) {  // same arithmetic as nms_gather_kernel
+      const float off = __fmul_rn((float)idxs[src], __fadd_rn(s_max, 1.f));
+      x1 = __fadd_rn(x1, off); y1 = __fadd_rn(y1, off);
+      x2 = __fadd_rn(x2, off); y2 = __fadd_rn(y2, off);
+    }
+    Box4f b;
+    b.x1 = x1; b.y1 = y1; b.x2 = x2; b.y2 = y2;
+    sorted[p] = b;
+    if (sorted_cls) sorted_cls[p] = (int32_t)idxs[src];
+  }
 }
 
 // ---- 4. IoU bit tiles ---------------------------------------------------------
@@ -658,16 +730,23 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
     B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairsDescending(
         L.cub_tmp, const_cast<size_t&>(L.cub_bytes), (const double*)L.keys_in, (double*)L.keys_out,
         (const int32_t*)L.idx_in, L.order, (int)n, 0, 64, st));
+  } else if (n <= kSortMax) {
+    if constexpr (!f64) {
+      nms_front_small_kernel<T><<<1, kSortThreads, 0, st>>>((const T*)boxes, (const T*)scores, idxs, (int)n, mode,
+                                                            (Box4f*)L.sorted, mode == 2 ? L.cls : nullptr, L.order);
+    }
   } else {
     nms_prepare_kernel<T><<<bl, th, 0, st>>>((const T*)scores, n, (float*)L.keys_in, L.idx_in);
     B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairsDescending(
         L.cub_tmp, const_cast<size_t&>(L.cub_bytes), (const float*)L.keys_in, (float*)L.keys_out,
         (const int32_t*)L.idx_in, L.order, (int)n, 0, 32, st));
   }
-  if (mode == 1)
-    nms_max_coord_kernel<T><<<1, 1024, 0, st>>>((const T*)boxes, n * 4, (A*)L.maxc);
-  nms_gather_kernel<T><<<bl, th, 0, st>>>((const T*)boxes, idxs, L.order, n, mode, (const A*)L.maxc,
-                                          (BoxT*)L.sorted, mode == 2 ? L.cls : nullptr);
+  if (f64 || n > kSortMax) {
+    if (mode == 1)
+      nms_max_coord_kernel<T><<<1, 1024, 0, st>>>((const T*)boxes, n * 4, (A*)L.maxc);
+    nms_gather_kernel<T><<<bl, th, 0, st>>>((const T*)boxes, idxs, L.order, n, mode, (const A*)L.maxc,
+                                            (BoxT*)L.sorted, mode == 2 ? L.cls : nullptr);
+  }
   dim3 grid((col_blocks + kColTiles - 1) / kColTiles, col_blocks);
   nms_mask_kernel<BoxT><<<grid, kTile, 0, st>>>((int)n, (float)thr, (const BoxT*)L.sorted,
                                                mode == 2 ? L.cls : nullptr, L.mask);

@@ -308,3 +308,26 @@ def test_iou_on_the_threshold_and_degenerate_boxes(capi):
     for mode, name in ((capi.BNMS_TRICK, "trick"), (capi.BNMS_VANILLA, "vanilla")):
         got = capi.batched_nms(grid[:600].to(DEV), s[:600].to(DEV), idx.to(DEV), 0.5, mode)
         assert torch.equal(got.cpu(), oracle.batched_nms(grid[:600], s[:600], idx, 0.5, name)), name
+
+
+@pytest.mark.parametrize("n", [7, 4096, 8191, 8192, 8193])
+def test_sort_front_ends_agree_with_the_oracle_on_special_scores(capi, n):
+    """Sets of up to 8192 boxes take the single-CTA sort, larger ones the device-wide radix sort: signed zeros,
+    infinities, long tie runs and 16-bit scores must rank the same way in both, i.e. like the oracle's stable
+    descending sort."""
+    g = torch.Generator().manual_seed(n)
+    b, _ = make_boxes(g, n, span=400.0)
+    s = torch.rand(n, generator=g)
+    s[::5] = 0.0
+    s[1::5] = -0.0
+    s[2::50] = float("inf")
+    s[3::50] = float("-inf")
+    s[4::9] = 0.25
+    s = s * torch.where(torch.rand(n, generator=g) < 0.3, -1.0, 1.0)
+    assert torch.equal(capi.nms(b.to(DEV), s.to(DEV), 0.5).cpu(), oracle.nms(b, s, 0.5))
+    idx = torch.randint(0, 6, (n,), generator=g)
+    for mode, name in ((capi.BNMS_TRICK, "trick"), (capi.BNMS_VANILLA, "vanilla")):
+        got = capi.batched_nms(b.to(DEV), s.to(DEV), idx.to(DEV), 0.5, mode)
+        assert torch.equal(got.cpu(), oracle.batched_nms(b, s, idx, 0.5, name)), name
+    bh, sh = b.half(), s.half()
+    assert torch.equal(capi.nms(bh.to(DEV), sh.to(DEV), 0.5).cpu(), oracle.nms(bh.float(), sh.float(), 0.5))
