@@ -866,22 +866,51 @@ __global__ void nms_seg_keys_kernel(const T* __restrict__ scores, const uint8_t*
 }
 
 // boxes.max() of every segment's surviving boxes (coordinate trick, boxes.py:91); one CTA per segment
+//
+// It also decides whether the segment may be scanned grouped by class (sgroup).  Grouping changes the greedy
+// order, so it needs classes that cannot interact.  The class compare of the vanilla strategy guarantees that;
+// the coordinate trick only does when the offsets idx * (max + 1) really separate the classes: all surviving
+// coordinates finite and >= 0 (so they lie in [0, max]) and |idx| * (max + 1) < 2^22, where consecutive offsets
+// differ by at least max after rounding (ulp <= 1/2) and x + offset rounds monotonically: boxes of different
+// classes then have inter = 0 exactly.  Otherwise the segment keeps the score order (all class keys 0).
 template <typename T>
-__global__ void nms_seg_max_kernel(const T* __restrict__ boxes, const uint8_t* __restrict__ valid,
-                                   const int32_t* __restrict__ off, float* __restrict__ out) {
+__global__ void nms_seg_max_kernel(const T* __restrict__ boxes, const int64_t* __restrict__ idxs,
+                                   const uint8_t* __restrict__ valid, const int32_t* __restrict__ off,
+                                   const int32_t* __restrict__ smode, float* __restrict__ out,
+                                   int32_t* __restrict__ sgroup) {
   __shared__ float red[32];
+  __shared__ int s_bad;
   const int s = blockIdx.x;
-  float m = -INFINITY;
-  bool nan = false;
+  if (smode[s] == 2) {
+    if (threadIdx.x == 0) sgroup[s] = 1;
+    return;
+  }
+  if (threadIdx.x == 0) s_bad = 0;
+  __syncthreads();
+  float m = -INFINITY, amax = 0.f;
+  bool nan = false, bad = false;
   for (int i = off[s] + threadIdx.x; i < off[s + 1]; i += blockDim.x) {
     if (valid && !valid[i]) continue;
+    amax = fmaxf(amax, fabsf((float)idxs[i]));
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       const float v = (float)Io<T>::ld(boxes + (long long)i * 4 + c);
       nan |= (v != v);
+      bad |= !(v >= 0.f && v < INFINITY);
       m = v > m ? v : m;
     }
   }
+  if (bad) atomicOr(&s_bad, 1);
+  for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = amax;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) amax = fmaxf(amax, red[w]);
+    red[0] = amax;
+  }
+  __syncthreads();
+  amax = red[0];
+  __syncthreads();
   if (nan) m = NAN;
   for (int o = 16; o > 0; o >>= 1) {
     const float other = __shfl_xor_sync(0xffffffffu, m, o);
@@ -895,23 +924,28 @@ __global__ void nms_seg_max_kernel(const T* __restrict__ boxes, const uint8_t* _
       const float other = __shfl_xor_sync(0xffffffffu, m, o);
       m = (other != other || m != m) ? NAN : (other > m ? other : m);
     }
-    if (threadIdx.x == 0) out[s] = m;
+    if (threadIdx.x == 0) {
+      out[s] = m;
+      sgroup[s] = (!s_bad && __fmul_rn(amax, __fadd_rn(m, 1.f)) < 4194304.f) ? 1 : 0;
+    }
   }
 }
 
 // Class key of a box: any order-preserving-for-equality map of the class id; filtered boxes go last
 __device__ __forceinline__ unsigned class_key(const int64_t* __restrict__ idxs, const uint8_t* __restrict__ valid,
-                                              long long src) {
+                                              long long src, int grouped) {
+  if (!grouped) return 0u;
   return (valid && !valid[src]) ? 0xffffffffu : ((unsigned)(int32_t)idxs[src] ^ 0x80000000u);
 }
 
 // second sort key of the class-grouped order: (segment, class key), applied stably to the score order
 __global__ void nms_seg_class_keys_kernel(const int64_t* __restrict__ idxs, const uint8_t* __restrict__ valid,
                                           const int32_t* __restrict__ order, int n, const int32_t* __restrict__ off,
-                                          int S, u64* __restrict__ keys) {
+                                          int S, const int32_t* __restrict__ sgroup, u64* __restrict__ keys) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  keys[i] = ((u64)(unsigned)seg_of(off, S, i) << 32) | (u64)class_key(idxs, valid, order[i]);
+  const int s = seg_of(off, S, i);
+  keys[i] = ((u64)(unsigned)s << 32) | (u64)class_key(idxs, valid, order[i], sgroup[s]);
 }
 
 // one warp per 64-box block of every segment: bounding box and class-key range
@@ -954,7 +988,8 @@ __global__ void nms_seg_gather_kernel(const T* __restrict__ boxes, const int64_t
                                       const int32_t* __restrict__ smode, const float* __restrict__ max_coord,
                                       Box4f* __restrict__ sorted, int32_t* __restrict__ sorted_cls,
                                       u64* __restrict__ init_remv, const int32_t* __restrict__ pos,
-                                      unsigned* __restrict__ ckey, int32_t* __restrict__ rank) {
+                                      const int32_t* __restrict__ sgroup, unsigned* __restrict__ ckey,
+                                      int32_t* __restrict__ rank) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int s = seg_of(off, S, i);
@@ -962,7 +997,7 @@ __global__ void nms_seg_gather_kernel(const T* __restrict__ boxes, const int64_t
   const long long src = order[sp];
   if (pos) {
     rank[i] = sp - off[s];
-    ckey[i] = class_key(idxs, valid, src);
+    ckey[i] = class_key(idxs, valid, src, sgroup[s]);
   }
   float x1 = (float)Io<T>::ld(boxes + src * 4 + 0), y1 = (float)Io<T>::ld(boxes + src * 4 + 1);
   float x2 = (float)Io<T>::ld(boxes + src * 4 + 2), y2 = (float)Io<T>::ld(boxes + src * 4 + 3);
@@ -984,7 +1019,7 @@ __global__ void nms_seg_gather_kernel(const T* __restrict__ boxes, const int64_t
 
 struct SegLayout {
   u64 *keys_in, *keys_out, *mask, *init_remv;
-  int32_t *idx_in, *order, *cls, *off, *roff, *smode, *pos, *rank;
+  int32_t *idx_in, *order, *cls, *off, *roff, *smode, *pos, *rank, *sgroup;
   unsigned* ckey;
   BlockSum* blk;
   long long* moff;
@@ -1016,6 +1051,7 @@ SegLayout seg_carve(void* ws, long long n, long long S, long long mask_words, lo
   L.off = (int32_t*)c.take((S + 1) * 4);
   L.roff = (int32_t*)c.take((S + 1) * 4);
   L.smode = (int32_t*)c.take((S + 1) * 4);
+  L.sgroup = (int32_t*)c.take((S + 1) * 4);
   L.moff = (long long*)c.take((S + 1) * 8);
   L.maxc = (float*)c.take((S + 1) * 4);
   L.sorted = (Box4f*)c.take(n * sizeof(Box4f));
@@ -1083,7 +1119,6 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
   B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairs(L.cub_tmp, const_cast<size_t&>(L.cub_bytes), (const u64*)L.keys_in,
                                                   L.keys_out, (const int32_t*)L.idx_in, L.order, (int)n, 0,
                                                   32 + seg_bits, st));
-  if (idxs && mode != 2) nms_seg_max_kernel<T><<<(unsigned)S, 256, 0, st>>>((const T*)boxes, valid, L.off, L.maxc);
   B200DET_CUDA_OK(cudaMemsetAsync(L.init_remv, 0, (size_t)(remv_words + 1) * 8, st));
   // Class-aware sets are scanned grouped by class: a second, stable sort of the score order by (segment, class)
   // makes the IoU mask block-diagonal, and whole tiles between different classes are skipped from the block
@@ -1091,15 +1126,17 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
   // different classes never suppress one another in either reference strategy, and where the coordinate trick
   // fails to separate them (negative or non-finite coordinates) the bounding boxes meet and the tile is computed.
   const bool grouped = idxs != nullptr && remv_words > 0;
+  if (idxs)
+    nms_seg_max_kernel<T><<<(unsigned)S, 256, 0, st>>>((const T*)boxes, idxs, valid, L.off, L.smode, L.maxc, L.sgroup);
   if (grouped) {
-    nms_seg_class_keys_kernel<<<bl, th, 0, st>>>(idxs, valid, L.order, (int)n, L.off, (int)S, L.keys_in);
+    nms_seg_class_keys_kernel<<<bl, th, 0, st>>>(idxs, valid, L.order, (int)n, L.off, (int)S, L.sgroup, L.keys_in);
     B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairs(L.cub_tmp, const_cast<size_t&>(L.cub_bytes),
                                                     (const u64*)L.keys_in, L.keys_out, (const int32_t*)L.idx_in, L.pos,
                                                     (int)n, 0, 32 + seg_bits, st));
   }
   nms_seg_gather_kernel<T><<<bl, th, 0, st>>>((const T*)boxes, idxs, valid, L.order, (int)n, L.off, L.roff, (int)S,
                                               L.smode, L.maxc, L.sorted, L.cls, L.init_remv,
-                                              grouped ? L.pos : nullptr, L.ckey, L.rank);
+                                              grouped ? L.pos : nullptr, L.sgroup, L.ckey, L.rank);
   if (grouped) {
     const int warps = (int)remv_words;
     nms_seg_blocks_kernel<<<(warps * 32 + th - 1) / th, th, 0, st>>>(L.sorted, L.ckey, L.off, L.roff, (int)S, warps,

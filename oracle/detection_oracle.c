@@ -271,7 +271,11 @@ API int64_t oracle_batched_nms_trick_f32(const float* boxes, const float* scores
                                          int thr_is_float, int64_t* keep) {
   if (n == 0) return 0;
   float mx = boxes[0];
-  for (int64_t i = 1; i < 4 * n; i++) mx = boxes[i] > mx ? boxes[i] : mx;
+  /* Tensor.max() propagates NaN: one NaN coordinate makes every offset NaN */
+  for (int64_t i = 1; i < 4 * n; i++) {
+    if (boxes[i] != boxes[i] || mx != mx) mx = NAN;
+    else mx = boxes[i] > mx ? boxes[i] : mx;
+  }
   const float m1 = mx + 1.0f;
   float* shifted = (float*)malloc((size_t)n * 4 * sizeof(float));
   for (int64_t i = 0; i < n; i++) {

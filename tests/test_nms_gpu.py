@@ -252,6 +252,42 @@ def test_segmented_auto_mode_and_negative_coordinates(capi):
         assert torch.equal(a.cpu(), w)
 
 
+@pytest.mark.parametrize("mode", ["trick", "vanilla"])
+def test_segmented_class_grouping_keeps_the_reference_result(capi, mode):
+    """Class-aware sets are scanned grouped by class with tiles between classes skipped.  The result must stay
+    the per-image batched_nms of the oracle when classes are many, ids are negative or large, boxes are filtered,
+    top-n cuts the list, and when the coordinate trick does NOT separate the classes (negative, infinite and NaN
+    coordinates) -- there the bounding-box test has to keep the tile."""
+    g = torch.Generator().manual_seed(91)
+    sizes = [1500, 0, 2300, 64, 129]
+    n = sum(sizes)
+    off = [0]
+    for z in sizes:
+        off.append(off[-1] + z)
+    b, s = make_boxes(g, n, span=150.0)
+    i = torch.randint(-3, 80, (n,), generator=g)
+    i[::97] = 2_000_000
+    valid = torch.rand(n, generator=g) > 0.25
+    m = {"trick": capi.BNMS_TRICK, "vanilla": capi.BNMS_VANILLA}[mode]
+    for variant in ("clean", "negative", "nonfinite"):
+        bb = b.clone()
+        if variant == "negative":
+            bb = bb - 400.0                       # offsets idx * (max + 1) no longer separate the classes
+        if variant == "nonfinite":
+            bb[5::301, 0] = float("nan")
+            bb[7::311, 3] = float("nan")
+            bb[11::401, 2] = float("inf")
+            bb[13::409, 0] = float("-inf")
+        for v, top_n in ((None, 0), (valid, 0), (valid, 100)):
+            want = _segmented_oracle(bb, s, i, off, 0.5, v, mode, top_n)
+            got = capi.nms_segmented(bb.to(DEV), s.to(DEV), i.to(DEV), off, 0.5,
+                                     valid=None if v is None else v.to(DEV), mode=m, top_n=top_n)
+            for k, (a, w) in enumerate(zip(got, want)):
+                assert torch.equal(a.cpu(), w), (mode, variant, k, top_n)
+        one = capi.batched_nms(bb[:1500].to(DEV), s[:1500].to(DEV), i[:1500].to(DEV), 0.5, m)
+        assert torch.equal(one.cpu(), oracle.batched_nms(bb[:1500], s[:1500], i[:1500], 0.5, mode)), (mode, variant)
+
+
 def test_segmented_equals_loop_of_batched_nms_full_size(capi):
     """64 images x 4663 RPN candidates (5 levels): one segmented call == 64 batched_nms calls."""
     g = torch.Generator().manual_seed(5)

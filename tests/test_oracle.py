@@ -231,3 +231,21 @@ def test_ps_roi_align_restatement_matches_compiled_reference(dtype):
             go = torch.randn(a.shape, generator=g, dtype=dtype)
             assert torch.equal(oracle.ps_roi_align_backward(go, rois, ma, scale, ph, pw, sr, *x.shape, impl="oracle"),
                                oracle.ps_roi_align_backward(go, rois, mb, scale, ph, pw, sr, *x.shape, impl="ref"))
+
+
+def test_batched_nms_trick_follows_tensor_max_on_nan():
+    """boxes.py:91 takes boxes.max(), which propagates NaN; the restatement must not skip NaN coordinates.
+    Checked against the trick written out in torch on top of the oracle's plain nms."""
+    g = torch.Generator().manual_seed(4)
+    n = 400
+    xy = torch.rand(n, 2, generator=g) * 100
+    b = torch.cat([xy, xy + torch.rand(n, 2, generator=g) * 40 + 5], 1)
+    s = torch.randperm(n, generator=g).float()
+    idx = torch.randint(0, 3, (n,), generator=g)
+    for where in (None, (0, 0), (123, 2)):
+        bb = b.clone()
+        if where is not None:
+            bb[where] = float("nan")
+        offsets = idx.to(bb) * (bb.max() + 1)
+        want = oracle.nms(bb + offsets[:, None], s, 0.5)
+        assert torch.equal(oracle.batched_nms(bb, s, idx, 0.5, "trick"), want), where
