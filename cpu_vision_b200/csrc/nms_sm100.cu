@@ -877,7 +877,7 @@ template <typename T>
 __global__ void nms_seg_max_kernel(const T* __restrict__ boxes, const int64_t* __restrict__ idxs,
                                    const uint8_t* __restrict__ valid, const int32_t* __restrict__ off,
                                    const int32_t* __restrict__ smode, float* __restrict__ out,
-                                   int32_t* __restrict__ sgroup) {
+                                   int32_t* __restrict__ sgroup, int thr_nonneg) {
   __shared__ float red[32];
   __shared__ int s_bad;
   const int s = blockIdx.x;
@@ -926,7 +926,8 @@ __global__ void nms_seg_max_kernel(const T* __restrict__ boxes, const int64_t* _
     }
     if (threadIdx.x == 0) {
       out[s] = m;
-      sgroup[s] = (!s_bad && __fmul_rn(amax, __fadd_rn(m, 1.f)) < 4194304.f) ? 1 : 0;
+      // a negative threshold lets disjoint boxes (IoU 0) suppress one another across classes
+      sgroup[s] = (thr_nonneg && !s_bad && __fmul_rn(amax, __fadd_rn(m, 1.f)) < 4194304.f) ? 1 : 0;
     }
   }
 }
@@ -1127,7 +1128,8 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
   // fails to separate them (negative or non-finite coordinates) the bounding boxes meet and the tile is computed.
   const bool grouped = idxs != nullptr && remv_words > 0;
   if (idxs)
-    nms_seg_max_kernel<T><<<(unsigned)S, 256, 0, st>>>((const T*)boxes, idxs, valid, L.off, L.smode, L.maxc, L.sgroup);
+    nms_seg_max_kernel<T><<<(unsigned)S, 256, 0, st>>>((const T*)boxes, idxs, valid, L.off, L.smode, L.maxc, L.sgroup,
+                                               (float)thr >= 0.f ? 1 : 0);
   if (grouped) {
     nms_seg_class_keys_kernel<<<bl, th, 0, st>>>(idxs, valid, L.order, (int)n, L.off, (int)S, L.sgroup, L.keys_in);
     B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairs(L.cub_tmp, const_cast<size_t&>(L.cub_bytes),

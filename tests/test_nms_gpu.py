@@ -284,6 +284,11 @@ def test_segmented_class_grouping_keeps_the_reference_result(capi, mode):
                                      valid=None if v is None else v.to(DEV), mode=m, top_n=top_n)
             for k, (a, w) in enumerate(zip(got, want)):
                 assert torch.equal(a.cpu(), w), (mode, variant, k, top_n)
+        for thr in (-0.5, 0.0):  # a negative threshold makes disjoint boxes of different classes interact
+            want = _segmented_oracle(bb, s, i, off, thr, valid, mode, 0)
+            got = capi.nms_segmented(bb.to(DEV), s.to(DEV), i.to(DEV), off, thr, valid=valid.to(DEV), mode=m)
+            for k, (a, w) in enumerate(zip(got, want)):
+                assert torch.equal(a.cpu(), w), (mode, variant, k, thr)
         one = capi.batched_nms(bb[:1500].to(DEV), s[:1500].to(DEV), i[:1500].to(DEV), 0.5, m)
         assert torch.equal(one.cpu(), oracle.batched_nms(bb[:1500], s[:1500], i[:1500], 0.5, mode)), (mode, variant)
 
