@@ -1,18 +1,17 @@
 // nms_sm100.cu -- greedy NMS and class-aware NMS, entirely on the device.
 //
 // Pipeline (all on the caller's stream, no host round trip):
-//   1. nms_prepare_kernel   scores -> fp32 sort keys, iota indices
-//                           (+ per-class coordinate offsets for the
-//                           coordinate-trick mode, torchvision/ops/boxes.py:91-93)
-//   2. cub::DeviceRadixSort::SortPairsDescending   stable, ties keep ascending
-//                           original index like scores.sort(stable=True,
-//                           descending=True) (cuda/nms_kernel.cu:112-113)
-//   3. nms_gather_kernel    boxes in score order, widened to the compare type
+//   1-3. up to 8192 boxes: nms_front_small_kernel -- ONE CTA builds the fp32 sort keys, block-radix-sorts
+//        them (stable: ties keep ascending original index like scores.sort(stable=True, descending=True),
+//        cuda/nms_kernel.cu:112-113), reduces boxes.max() for the coordinate trick (boxes.py:91-93) and
+//        gathers the boxes into score order.  Larger sets / fp64 scores: nms_prepare_kernel,
+//        cub::DeviceRadixSort::SortPairsDescending, nms_max_coord_kernel, nms_gather_kernel.
 //   4. nms_mask_kernel      upper-triangular 64x64 IoU>thr bit tiles
 //                           (replaces nms_kernel_impl, cuda/nms_kernel.cu:31-78)
-//   5. nms_scan_kernel      greedy keep scan on the device, one CTA
-//                           (replaces the D2H copy + host loop, :136-159) and
+//   5. nms_scan_smem_kernel / nms_scan_kernel   greedy keep scan on the device, one CTA
+//                           (replaces the D2H copy + host loop, :136-159);
 //                           writes keep[] = order[kept] and the count.
+// Segmented (per-image) variant: see "segmented NMS" below.
 //
 // IoU follows devIoU (cuda/nms_kernel.cu:16-29) with every operation an
 // explicit round-to-nearest intrinsic so no FMA contraction can change a
