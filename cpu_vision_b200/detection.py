@@ -30,6 +30,17 @@ def _require_cuda(t: Tensor, who: str):
         raise RuntimeError(f"cpu_vision_b200.{who}: tensors must be CUDA tensors (no CPU fallback)")
 
 
+def _gather_kept(keep: Tensor, counts: Tensor, off: Sequence[int], *tensors: Tensor) -> List[List[Tensor]]:
+    """Per-image results from the segmented keep buffer: ONE read-back of the S counts, one concatenation of
+    the kept index ranges and one gather per result tensor; the per-image tensors are views of those (the
+    reference's loops launch an indexing kernel per image and result)."""
+    c = counts.tolist()
+    if not c:
+        return [[] for _ in tensors]
+    allk = torch.cat([keep[off[s]: off[s] + c[s]] for s in range(len(c))])
+    return [list(t[allk].split(c)) for t in tensors]
+
+
 def _get_top_n_idx(objectness: Tensor, num_anchors_per_level: Sequence[int], pre_nms_top_n: int) -> Tensor:
     """rpn.py:231-240: top-k per level, indices into the concatenated anchors."""
     r, offset = [], 0
@@ -65,9 +76,10 @@ def filter_proposals(proposals: Tensor, objectness: Tensor, image_shapes: List[T
     boxes, valid = capi.clip_filter_boxes(proposals.reshape(-1, 4), scores.reshape(-1), off, image_shapes, min_size,
                                           score_thresh, strict=False)
     flat_scores = scores.reshape(-1).contiguous()
-    keeps = capi.nms_segmented(boxes, flat_scores, levels.reshape(-1), off, nms_thresh, valid=valid,
-                               top_n=post_nms_top_n)
-    return [boxes[k] for k in keeps], [flat_scores[k] for k in keeps]
+    keep, counts = capi.nms_segmented(boxes, flat_scores, levels.reshape(-1), off, nms_thresh, valid=valid,
+                                      top_n=post_nms_top_n, sync=False)
+    final_boxes, final_scores = _gather_kept(keep, counts, off, boxes, flat_scores)
+    return final_boxes, final_scores
 
 
 def decode_boxes(rel_codes: Tensor, boxes: Tensor, weights: Sequence[float],
@@ -115,5 +127,7 @@ def postprocess_detections(class_logits: Tensor, box_regression: Tensor, proposa
     for n in boxes_per_image:
         off.append(off[-1] + n * (num_classes - 1))
     boxes, valid = capi.clip_filter_boxes(boxes, scores, off, image_shapes, 1e-2, score_thresh, strict=True)
-    keeps = capi.nms_segmented(boxes, scores, labels, off, nms_thresh, valid=valid, top_n=detections_per_img)
-    return [boxes[k] for k in keeps], [scores[k] for k in keeps], [labels[k] for k in keeps]
+    keep, counts = capi.nms_segmented(boxes, scores, labels, off, nms_thresh, valid=valid, top_n=detections_per_img,
+                                      sync=False)
+    all_boxes, all_scores, all_labels = _gather_kept(keep, counts, off, boxes, scores, labels)
+    return all_boxes, all_scores, all_labels
