@@ -30,6 +30,17 @@ namespace {
 typedef unsigned long long u64;
 constexpr int kTile = 64;
 
+// Mask layout: upper-triangular, packed by row block.  Row block b keeps, for each of its 64 rows, only the
+// words of column blocks j >= b: block base 64 * (b * cb - b (b - 1) / 2) words, row stride cb - b.  The rows of
+// a block stay contiguous (one bulk copy stages them in the scan) and carry no words left of the diagonal,
+// which halves what the scan reads.  Bases are multiples of 512 bytes.
+__host__ __device__ __forceinline__ long long tri_base(int b, int cb) {
+  return (long long)kTile * ((long long)b * cb - (long long)b * (b - 1) / 2);
+}
+__host__ __device__ __forceinline__ long long tri_word(int b, int i, int j, int cb) {
+  return tri_base(b, cb) + (long long)i * (cb - b) + (j - b);
+}
+
 struct alignas(16) Box4f { float x1, y1, x2, y2; };
 struct alignas(32) Box4d { double x1, y1, x2, y2; };
 
@@ -304,7 +315,7 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
     if (col_start < row_start) continue;
     const int col_size = min(n - col_start * kTile, kTile);
     if (blk && tile_is_empty(blk[row_start], blk[col_start], skip_apart, cls != nullptr)) {  // CTA-uniform
-      if (have_row) mask[(long long)cur * col_blocks + col_start] = 0ULL;
+      if (have_row) mask[tri_word(row_start, threadIdx.x, col_start, col_blocks)] = 0ULL;
       continue;
     }
     __syncthreads();  // the previous tile's columns are no longer read
@@ -325,7 +336,7 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
         valid &= start >= kTile ? 0ULL : (~0ULL << start);
         w = cls ? tile_bits_f32<true>(a, sa, ac, cb, carea, cc, thr, valid)
                 : tile_bits_f32<false>(a, sa, ac, cb, carea, cc, thr, valid);
-        mask[(long long)cur * col_blocks + col_start] = w;
+        mask[tri_word(row_start, threadIdx.x, col_start, col_blocks)] = w;
         continue;
       }
     }
@@ -334,7 +345,7 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
       if (skip_apart && !boxes_meet(a, cb[i])) continue;
       if (iou_gt(a, cb[i], thr)) w |= 1ULL << i;
     }
-    mask[(long long)cur * col_blocks + col_start] = w;
+    mask[tri_word(row_start, threadIdx.x, col_start, col_blocks)] = w;
   }
 }
 
@@ -507,17 +518,18 @@ __device__ __forceinline__ u64 resolve_block_warp(u64 alive, u64 d0, u64 d1, int
 // unrolled so the loads of the kept rows are independent and pipelined
 template <int RPG>
 __device__ __forceinline__ void or_rows(const u64* __restrict__ rowsb, u64* remv, u64 kept, int j0, int col_blocks,
-                                        int t) {
+                                        int t, int b) {
+  const int stride = col_blocks - b;  // staged rows start at column block b
   constexpr int kGroups = kTile / RPG, kPer = (kSmemThreads - 32) / kGroups;
   const int q = t / kPer;
   const unsigned kq = (unsigned)(kept >> (q * RPG)) & (RPG == 32 ? 0xffffffffu : ((1u << RPG) - 1u));
   if (!kq) return;
   for (int j = j0 + (t - q * kPer); j < col_blocks; j += kPer) {
-    const u64* col = rowsb + (size_t)(q * RPG) * col_blocks + j;
+    const u64* col = rowsb + (size_t)(q * RPG) * stride + (j - b);
     u64 acc = 0;
 #pragma unroll
     for (int i = 0; i < RPG; ++i) {
-      if ((kq >> i) & 1u) acc |= col[(size_t)i * col_blocks];  // predicated loads: dropped rows cost no bandwidth
+      if ((kq >> i) & 1u) acc |= col[(size_t)i * stride];  // predicated loads: dropped rows cost no bandwidth
     }
     // two 32-bit shared atomics: a 64-bit OR on shared memory is a CAS loop, and the groups meet here
     unsigned* w = reinterpret_cast<unsigned*>(remv + j);
@@ -548,23 +560,24 @@ __device__ __forceinline__ void scan_smem_body(
   __syncthreads();
 
   // rows of block b (all 64 are real for every block but the last, whose rows nobody reads): contiguous in the
-  // mask, so one bulk copy.  The words left of the diagonal ride along: a bulk copy per row for only the right
-  // part was measured at ~60 cycles of issue per copy (3900 cycles per block), far worse than the extra bytes.
+  // packed-triangular mask and free of words left of the diagonal, so one bulk copy moves exactly what is read.
+  // (With a row-major mask, a bulk copy per row for only the right part was measured at ~60 cycles of issue
+  // per copy, 3900 cycles per block.)
   auto prefetch_rows = [&](int b) {  // one thread
     if (b + 1 >= col_blocks) return;
-    const unsigned bytes = (unsigned)(kTile * col_blocks * sizeof(u64));
+    const unsigned bytes = (unsigned)(kTile * (col_blocks - b) * sizeof(u64));
     const unsigned bar = smem_u32(&s_bar[b & 1]);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic reads of this stage are done
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(stage + (size_t)(b & 1) * kTile * col_blocks)),
-                   "l"(mask + (size_t)b * kTile * col_blocks), "r"(bytes), "r"(bar) : "memory");
+                   "l"(mask + tri_base(b, col_blocks)), "r"(bytes), "r"(bar) : "memory");
   };
   auto prefetch_diag = [&](int b, int i) {  // mask[b*64 + i][b], i < rows
     if (b >= col_blocks || i >= min(n - b * kTile, kTile)) return;
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;"
                  ::"r"(smem_u32(ring + (b & (kDiagRing - 1)) * kTile + i)),
-                   "l"(mask + (size_t)(b * kTile + i) * col_blocks + b) : "memory");
+                   "l"(mask + tri_word(b, i, b, col_blocks)) : "memory");
   };
   auto resolve = [&](int b, u64 removed) {  // warp 0, all lanes
     const int rows = min(n - b * kTile, kTile);
@@ -606,8 +619,8 @@ __device__ __forceinline__ void scan_smem_body(
       if (b + 1 < col_blocks) {
         // word b+1 of the kept rows of block b: two rows per lane, OR across the warp
         u64 v = 0;
-        if ((kept >> lane) & 1ULL) v |= rowsb[(size_t)lane * col_blocks + b + 1];
-        if ((kept >> (lane + 32)) & 1ULL) v |= rowsb[(size_t)(lane + 32) * col_blocks + b + 1];
+        if ((kept >> lane) & 1ULL) v |= rowsb[(size_t)lane * (col_blocks - b) + 1];
+        if ((kept >> (lane + 32)) & 1ULL) v |= rowsb[(size_t)(lane + 32) * (col_blocks - b) + 1];
         const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v);
         const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
         SCAN_T(3)
@@ -619,10 +632,10 @@ __device__ __forceinline__ void scan_smem_body(
       // OR the kept rows into the words right of b+1: G thread groups take 64 / G rows each, a thread strides
       // over the words; more groups as fewer words remain
       const int ncols = col_blocks - (b + 2), t = tid - 32;
-      if (ncols > 120) or_rows<32>(rowsb, remv, kept, b + 2, col_blocks, t);
-      else if (ncols > 60) or_rows<16>(rowsb, remv, kept, b + 2, col_blocks, t);
-      else if (ncols > 30) or_rows<8>(rowsb, remv, kept, b + 2, col_blocks, t);
-      else or_rows<4>(rowsb, remv, kept, b + 2, col_blocks, t);
+      if (ncols > 120) or_rows<32>(rowsb, remv, kept, b + 2, col_blocks, t, b);
+      else if (ncols > 60) or_rows<16>(rowsb, remv, kept, b + 2, col_blocks, t, b);
+      else if (ncols > 30) or_rows<8>(rowsb, remv, kept, b + 2, col_blocks, t, b);
+      else or_rows<4>(rowsb, remv, kept, b + 2, col_blocks, t, b);
     }
     if (warp != 0) { SCAN_T(3) }
   }
@@ -668,7 +681,7 @@ __device__ __forceinline__ void scan_body(
 
   for (int b = 0; b < col_blocks; ++b) {
     const int rows = min(n - b * kTile, kTile);
-    if (tid < kTile) diag[tid] = tid < rows ? mask[(long long)(b * kTile + tid) * col_blocks + b] : 0ULL;
+    if (tid < kTile) diag[tid] = tid < rows ? mask[tri_word(b, tid, b, col_blocks)] : 0ULL;
     __syncthreads();
     if (tid == 0) {
       u64 alive = ~remv[b];
@@ -685,7 +698,7 @@ __device__ __forceinline__ void scan_body(
       while (kk) {
         const int i = __ffsll((long long)kk) - 1;
         kk &= kk - 1;
-        acc |= mask[(long long)(b * kTile + i) * col_blocks + j];
+        acc |= mask[tri_word(b, i, j, col_blocks)];
       }
       remv[j] = acc;
     }
