@@ -393,7 +393,7 @@ __global__ void __launch_bounds__(kTile) nms_seg_mask_kernel(const int32_t* __re
 // nms_scan_kernel (any N): rows of kept boxes are read from global memory.
 constexpr int kScanThreads = 1024;
 constexpr int kSmemThreads = 512;
-constexpr int kSmemBlocks = 208;  // 1040 bytes of shared memory per block + 2 KB of diagonal ring: 213 KB
+constexpr int kSmemBlocks = 208;  // 1064 bytes of shared memory per block + 2 KB of diagonal ring: 218 KB
 
 __device__ __forceinline__ u64 resolve_block(u64 alive, const u64* __restrict__ diag, int stride) {
   u64 d[kTile];
@@ -514,27 +514,33 @@ __device__ __forceinline__ u64 resolve_block_warp(u64 alive, u64 d0, u64 d1, int
   }
 }
 
-// OR phase of one block for the kSmemThreads - 32 worker threads: group q takes rows [q * RPG, (q + 1) * RPG),
-// unrolled so the loads of the kept rows are independent and pipelined
-template <int RPG>
+// OR phase of one block for worker warps 1..15.  remv is kept as kRowGroups partial words per column block:
+// a unit of work is (row group g of 16 rows, 32 consecutive column blocks), its lanes read one row segment at
+// a time (conflict-free) and OR into remv[g][j] with a plain read-modify-write -- each (g, j) has exactly one
+// writer per block, so no atomics, and the resolver warp folds the partials of the one column it needs into
+// the warp reduction it does anyway.  Measured alternatives: row groups meeting in shared atomics 670 cycles
+// per block; one thread per column with 64 loads 1200-1500 (ptxas keeps two shared loads in flight at ~23
+// cycles each whatever the source says, so warps have to hide the latency, not unrolling); row groups inside
+// a warp combined by shuffles 1000 (the groups' row segments are 16 * stride words apart: 4-way bank conflicts).
+constexpr int kRowGroups = 4, kGroupRows = kTile / kRowGroups;
+
 __device__ __forceinline__ void or_rows(const u64* __restrict__ rowsb, u64* remv, u64 kept, int j0, int col_blocks,
-                                        int t, int b) {
+                                        int warp, int lane, int b) {
+  constexpr int kWorkers = kSmemThreads / 32 - 1;
   const int stride = col_blocks - b;  // staged rows start at column block b
-  constexpr int kGroups = kTile / RPG, kPer = (kSmemThreads - 32) / kGroups;
-  const int q = t / kPer;
-  const unsigned kq = (unsigned)(kept >> (q * RPG)) & (RPG == 32 ? 0xffffffffu : ((1u << RPG) - 1u));
-  if (!kq) return;
-  for (int j = j0 + (t - q * kPer); j < col_blocks; j += kPer) {
-    const u64* col = rowsb + (size_t)(q * RPG) * stride + (j - b);
+  const int units = ((col_blocks - j0 + 31) / 32) * kRowGroups;
+  for (int u = warp - 1; u < units; u += kWorkers) {  // warp-uniform
+    const int g = u % kRowGroups, j = j0 + (u / kRowGroups) * 32 + lane;
+    const unsigned kq = (unsigned)(kept >> (kGroupRows * g)) & ((1u << kGroupRows) - 1u);
+    if (!kq || j >= col_blocks) continue;
+    const u64* col = rowsb + (size_t)(kGroupRows * g) * stride + (j - b);
     u64 acc = 0;
 #pragma unroll
-    for (int i = 0; i < RPG; ++i) {
-      if ((kq >> i) & 1u) acc |= col[(size_t)i * stride];  // predicated loads: dropped rows cost no bandwidth
+    for (int i = 0; i < kGroupRows; ++i) {
+      const u64 v = col[(size_t)i * stride];
+      acc |= ((kq >> i) & 1u) ? v : 0ULL;
     }
-    // two 32-bit shared atomics: a 64-bit OR on shared memory is a CAS loop, and the groups meet here
-    unsigned* w = reinterpret_cast<unsigned*>(remv + j);
-    if ((unsigned)acc) atomicOr(w, (unsigned)acc);
-    if ((unsigned)(acc >> 32)) atomicOr(w + 1, (unsigned)(acc >> 32));
+    if (acc) remv[g * col_blocks + j] |= acc;
   }
 }
 
@@ -543,15 +549,16 @@ __device__ __forceinline__ void scan_smem_body(
     int64_t* __restrict__ keep, int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n,
     const int32_t* __restrict__ rank = nullptr) {
   extern __shared__ __align__(16) u64 smem[];
-  u64* remv = smem;                                    // [col_blocks]
-  u64* keptw = smem + col_blocks;                      // [col_blocks]
-  u64* ring = smem + 2 * col_blocks;                   // [kDiagRing][kTile] diagonal words
-  u64* stage = ring + kDiagRing * kTile;               // [2][kTile * col_blocks], 16-byte aligned
+  u64* remv = smem;                                    // [kRowGroups][col_blocks] partial words, OR = removed
+  u64* keptw = smem + kRowGroups * col_blocks;         // [col_blocks]
+  u64* ring = keptw + col_blocks;                      // [kDiagRing][kTile] diagonal words
+  u64* stage = ring + kDiagRing * kTile + (col_blocks & 1);  // [2][kTile * col_blocks], on an even word (16 B)
   __shared__ __align__(8) u64 s_bar[2];
   __shared__ u64 s_kept;
   __shared__ int s_base[32];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int j = tid; j < col_blocks; j += kSmemThreads) remv[j] = init_remv ? init_remv[j] : 0ULL;
+  for (int j = tid; j < kRowGroups * col_blocks; j += kSmemThreads)
+    remv[j] = (init_remv && j < col_blocks) ? init_remv[j] : 0ULL;
   if (tid == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[0])) : "memory");
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[1])) : "memory");
@@ -587,16 +594,17 @@ __device__ __forceinline__ void scan_smem_body(
     return resolve_block_warp(alive, d[lane], d[lane + 32], lane);
   };
 
-  if (tid == 32) prefetch_rows(0);
-  if (tid >= 64 && tid < 64 + kTile) {
-    prefetch_diag(0, tid - 64);
-    prefetch_diag(1, tid - 64);
+  if (tid == kSmemThreads - 32) prefetch_rows(0);
+  constexpr int kDiagT0 = kSmemThreads - 32 - kTile;  // the two warps before the last fetch diagonal words
+  if (tid >= kDiagT0 && tid < kDiagT0 + kTile) {
+    prefetch_diag(0, tid - kDiagT0);
+    prefetch_diag(1, tid - kDiagT0);
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
   if (warp == 0) {
-    const u64 k0 = resolve(0, remv[0]);
+    const u64 k0 = resolve(0, remv[0]);  // nothing has been ORed in yet: group 0 holds init_remv
     if (lane == 0) keptw[0] = k0;
   }
 #ifdef B200DET_SCAN_PROFILE
@@ -609,8 +617,8 @@ __device__ __forceinline__ void scan_smem_body(
     SCAN_T(0)
     __syncthreads();  // OR phase of block b-1 done; keptw[b] and diag(b+1) visible
     SCAN_T(1)
-    if (tid == 32) prefetch_rows(b + 1);  // into the stage block b-1 has left
-    if (tid >= 64 && tid < 64 + kTile) prefetch_diag(b + 2, tid - 64);
+    if (tid == kSmemThreads - 32) prefetch_rows(b + 1);  // into the stage block b-1 has left (last warp: no OR work)
+    if (tid >= kDiagT0 && tid < kDiagT0 + kTile) prefetch_diag(b + 2, tid - kDiagT0);
     asm volatile("cp.async.commit_group;" ::: "memory");
     SCAN_T(2)
     const u64 kept = keptw[b];
@@ -621,21 +629,16 @@ __device__ __forceinline__ void scan_smem_body(
         u64 v = 0;
         if ((kept >> lane) & 1ULL) v |= rowsb[(size_t)lane * (col_blocks - b) + 1];
         if ((kept >> (lane + 32)) & 1ULL) v |= rowsb[(size_t)(lane + 32) * (col_blocks - b) + 1];
+        if (lane < kRowGroups) v |= remv[lane * col_blocks + b + 1];  // the partial words of that column
         const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v);
         const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
         SCAN_T(3)
-        const u64 k1 = resolve(b + 1, remv[b + 1] | ((u64)hi << 32) | (u64)lo);
+        const u64 k1 = resolve(b + 1, ((u64)hi << 32) | (u64)lo);
         if (lane == 0) keptw[b + 1] = k1;
         SCAN_T(4)
       }
     } else if (kept && b + 2 < col_blocks) {
-      // OR the kept rows into the words right of b+1: G thread groups take 64 / G rows each, a thread strides
-      // over the words; more groups as fewer words remain
-      const int ncols = col_blocks - (b + 2), t = tid - 32;
-      if (ncols > 120) or_rows<32>(rowsb, remv, kept, b + 2, col_blocks, t, b);
-      else if (ncols > 60) or_rows<16>(rowsb, remv, kept, b + 2, col_blocks, t, b);
-      else if (ncols > 30) or_rows<8>(rowsb, remv, kept, b + 2, col_blocks, t, b);
-      else or_rows<4>(rowsb, remv, kept, b + 2, col_blocks, t, b);
+      or_rows(rowsb, remv, kept, b + 2, col_blocks, warp, lane, b);
     }
     if (warp != 0) { SCAN_T(3) }
   }
@@ -810,7 +813,7 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
   nms_mask_kernel<BoxT><<<grid, kTile, 0, st>>>((int)n, (float)thr, (const BoxT*)L.sorted,
                                                mode == 2 ? L.cls : nullptr, L.mask);
   if (col_blocks <= kSmemBlocks) {
-    const size_t smem = ((size_t)2 * col_blocks + kDiagRing * kTile + (size_t)2 * kTile * col_blocks) * sizeof(u64);
+    const size_t smem = ((size_t)(kRowGroups + 1) * col_blocks + 1 + kDiagRing * kTile + (size_t)2 * kTile * col_blocks) * sizeof(u64);
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     nms_scan_smem_kernel<<<1, kSmemThreads, smem, st>>>(L.mask, (int)n, col_blocks, L.order, keep, num_keep);
@@ -1163,7 +1166,7 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
                                                        L.roff, grouped ? L.blk : nullptr);
   }
   if (cb_max <= kSmemBlocks) {
-    const size_t smem = ((size_t)2 * cb_max + kDiagRing * kTile + (size_t)2 * kTile * cb_max) * sizeof(u64) + 16;
+    const size_t smem = ((size_t)(kRowGroups + 1) * cb_max + 1 + kDiagRing * kTile + (size_t)2 * kTile * cb_max) * sizeof(u64) + 16;
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_seg_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     nms_seg_scan_smem_kernel<<<(unsigned)S, kSmemThreads, smem, st>>>(L.mask, L.off, L.moff, L.roff, L.order, keep,
