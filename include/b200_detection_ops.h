@@ -176,7 +176,8 @@ int b200det_nms(
 
 /* Class-aware NMS in one pass.  Replaces batched_nms
  * (torchvision/ops/boxes.py:44-112).
- *   idxs : device int64 [N] category of each box
+ *   idxs : device int64 [N] category of each box (the per-class compare of the VANILLA strategy and the
+ *          class grouping of b200det_nms_segmented use the low 32 bits: ids must be distinct modulo 2^32)
  *   mode : b200det_bnms_mode.  COORD_TRICK reproduces the fp32 rounding of
  *          `boxes + idxs.to(boxes) * (boxes.max() + 1)`; VANILLA compares the
  *          unshifted boxes class by class. */
