@@ -10,7 +10,8 @@ which the reference runs as a Python loop over images: per image clip -> two fil
 stay static: one ``b200det_clip_filter_boxes`` pass writes the clipped boxes and a validity byte per
 box for ALL images, one ``b200det_nms_segmented`` call runs every image's class-aware NMS
 concurrently (one scan CTA per image), and a single read-back of the per-image counts at the very end
-sizes the output lists.  Per-level top-k (``Tensor.topk``), sigmoid / softmax and the BoxCoder
+sizes the output lists.  (``postprocess_detections`` compacts the survivors of the score filter before
+NMS -- one more read-back -- because there the filter drops ~99 % of the instances.)  Per-level top-k (``Tensor.topk``), sigmoid / softmax and the BoxCoder
 arithmetic are library element-wise ops, written in the reference's operation order.
 
 No CPU fallback: CUDA tensors only.
@@ -127,7 +128,15 @@ def postprocess_detections(class_logits: Tensor, box_regression: Tensor, proposa
     for n in boxes_per_image:
         off.append(off[-1] + n * (num_classes - 1))
     boxes, valid = capi.clip_filter_boxes(boxes, scores, off, image_shapes, 1e-2, score_thresh, strict=True)
-    keep, counts = capi.nms_segmented(boxes, scores, labels, off, nms_thresh, valid=valid, top_n=detections_per_img,
-                                      sync=False)
-    all_boxes, all_scores, all_labels = _gather_kept(keep, counts, off, boxes, scores, labels)
+    # The score filter drops most of the (proposal, class) instances (1000 proposals x 90 classes per image,
+    # a few hundred above 0.05) and NMS is quadratic in the set size, so unlike the RPN side -- where nearly
+    # every candidate survives and the shapes stay static -- the survivors are compacted first: ONE read-back of
+    # the per-image survivor counts (the reference synchronises per image at boxes[inds]).
+    csum = torch.cat([valid.new_zeros(1, dtype=torch.int64), valid.cumsum(0, dtype=torch.int64)])
+    ends = csum[torch.tensor(off, device=device)].tolist()
+    off2 = [e - ends[0] for e in ends]
+    vidx = valid.nonzero().squeeze(1)
+    boxes, scores, labels = boxes[vidx], scores[vidx], labels[vidx]
+    keep, counts = capi.nms_segmented(boxes, scores, labels, off2, nms_thresh, top_n=detections_per_img, sync=False)
+    all_boxes, all_scores, all_labels = _gather_kept(keep, counts, off2, boxes, scores, labels)
     return all_boxes, all_scores, all_labels
