@@ -485,6 +485,21 @@ def secondary_legs(capi, dev, peak):
 
     loop_ms = timed(loop, iters=3, flush_l2=False)
     del props, obj, ctr, wh, pb, ps, lv, pbf, psf, lvf
+    # cfg5 (RoIHeads side): postprocess_detections for 64 images x 1000 proposals x 91 classes (roi_heads defaults:
+    # score 0.05, NMS 0.5, 100 detections per image): softmax / box decoding (library element-wise ops), clip +
+    # filters, compaction of the survivors, ONE segmented class-aware NMS, top-100
+    P_, C_ = 1000, 91
+    rp = []
+    for _ in range(B):
+        c_ = torch.rand(P_, 2, generator=gen, device=dev) * torch.tensor([1088.0, 800.0], device=dev)
+        w_ = torch.exp(torch.rand(P_, 2, generator=gen, device=dev) * 3.0 + 2.5)
+        rp.append(torch.cat([c_ - w_ / 2, c_ + w_ / 2], 1))
+    lg = torch.randn(B * P_, C_, generator=gen, device=dev) * 2.5
+    rg = torch.randn(B * P_, C_ * 4, generator=gen, device=dev) * 0.5
+    f1b_ms = timed(lambda: detection.postprocess_detections(lg, rg, rp, shapes, 0.05, 0.5, 100), iters=5,
+                   flush_l2=False)
+    det_n = sum(b_.shape[0] for b_ in detection.postprocess_detections(lg, rg, rp, shapes, 0.05, 0.5, 100)[0])
+    del rp, lg, rg
     # cfg3 as an NCHW caller sees it (the reference's models hand NCHW-contiguous features to roi_align):
     # the dispatcher shim re-lays out -> channels_last kernels -> re-lays out; results are NCHW-contiguous
     import cpu_vision_b200  # noqa: F401
@@ -508,6 +523,9 @@ def secondary_legs(capi, dev, peak):
         "filter_proposals_boxes_per_s": B * per / (f1_ms / 1e3),
         "nms_segmented_ms": seg_ms, "nms_segmented_boxes_per_s": B * per / (seg_ms / 1e3),
         "per_image_loop_of_batched_nms_ms": loop_ms, "speedup_vs_loop": loop_ms / seg_ms}
+    res["cfg5_roi_heads_postprocess_64img"] = {
+        "instances_per_image": P_ * (C_ - 1), "postprocess_detections_ms": f1b_ms,
+        "instances_per_s": B * P_ * (C_ - 1) / (f1b_ms / 1e3), "detections": det_n}
     return res
 
 
