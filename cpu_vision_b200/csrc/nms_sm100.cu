@@ -37,9 +37,22 @@ constexpr int kTile = 64;
 __host__ __device__ __forceinline__ long long tri_base(int b, int cb) {
   return (long long)kTile * ((long long)b * cb - (long long)b * (b - 1) / 2);
 }
-__host__ __device__ __forceinline__ long long tri_word(int b, int i, int j, int cb) {
-  return tri_base(b, cb) + (long long)i * (cb - b) + (j - b);
-}
+
+// Class-grouped sets cut every block row at its last live tile jmax[b] (nothing right of it can hold a bit):
+// row stride jmax[b] - b + 1, block bases from a prefix sum (wbase, in units of 64 words).  jmax == nullptr
+// is the plain triangular layout.
+struct MaskIdx {
+  const int32_t* jmax;
+  const int32_t* wbase;
+  int cb;
+  __device__ __forceinline__ int width(int b) const { return jmax ? jmax[b] - b + 1 : cb - b; }
+  __device__ __forceinline__ long long base(int b) const {
+    return jmax ? (long long)kTile * wbase[b] : tri_base(b, cb);
+  }
+  __device__ __forceinline__ long long word(int b, int i, int j) const {
+    return base(b) + (long long)i * width(b) + (j - b);
+  }
+};
 
 struct alignas(16) Box4f { float x1, y1, x2, y2; };
 struct alignas(32) Box4d { double x1, y1, x2, y2; };
@@ -294,7 +307,10 @@ __device__ __forceinline__ bool tile_is_empty(const BlockSum& r, const BlockSum&
 template <typename BoxT>
 __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restrict__ boxes,
                                            const int32_t* __restrict__ cls, u64* __restrict__ mask,
-                                           int row_start, int col_group, const BlockSum* __restrict__ blk = nullptr) {
+                                           int row_start, int col_group, const BlockSum* __restrict__ blk = nullptr,
+                                           const int32_t* __restrict__ jmax = nullptr,
+                                           const int32_t* __restrict__ wbase = nullptr) {
+  const MaskIdx mi{jmax, wbase, (n + kTile - 1) / kTile};
   const int col_blocks = (n + kTile - 1) / kTile;
   const int row_size = min(n - row_start * kTile, kTile);
   __shared__ BoxT cb[kTile];
@@ -314,8 +330,9 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
     if (col_start >= col_blocks) break;
     if (col_start < row_start) continue;
     const int col_size = min(n - col_start * kTile, kTile);
+    if (jmax && col_start > jmax[row_start]) break;  // right of the block's last live tile: the scan never reads it
     if (blk && tile_is_empty(blk[row_start], blk[col_start], skip_apart, cls != nullptr)) {  // CTA-uniform
-      if (have_row) mask[tri_word(row_start, threadIdx.x, col_start, col_blocks)] = 0ULL;
+      if (have_row) mask[mi.word(row_start, threadIdx.x, col_start)] = 0ULL;
       continue;
     }
     __syncthreads();  // the previous tile's columns are no longer read
@@ -336,7 +353,7 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
         valid &= start >= kTile ? 0ULL : (~0ULL << start);
         w = cls ? tile_bits_f32<true>(a, sa, ac, cb, carea, cc, thr, valid)
                 : tile_bits_f32<false>(a, sa, ac, cb, carea, cc, thr, valid);
-        mask[tri_word(row_start, threadIdx.x, col_start, col_blocks)] = w;
+        mask[mi.word(row_start, threadIdx.x, col_start)] = w;
         continue;
       }
     }
@@ -345,7 +362,7 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
       if (skip_apart && !boxes_meet(a, cb[i])) continue;
       if (iou_gt(a, cb[i], thr)) w |= 1ULL << i;
     }
-    mask[tri_word(row_start, threadIdx.x, col_start, col_blocks)] = w;
+    mask[mi.word(row_start, threadIdx.x, col_start)] = w;
   }
 }
 
@@ -368,14 +385,16 @@ __global__ void __launch_bounds__(kTile) nms_seg_mask_kernel(const int32_t* __re
                                                              const int32_t* __restrict__ cls,
                                                              u64* __restrict__ mask,
                                                              const int32_t* __restrict__ roff,
-                                                             const BlockSum* __restrict__ blk) {
+                                                             const BlockSum* __restrict__ blk,
+                                                             const int32_t* __restrict__ jmax,
+                                                             const int32_t* __restrict__ wbase) {
   const int s = blockIdx.z;
   const int o = off[s], n = off[s + 1] - o;
   const int row_start = blockIdx.y, col_group = blockIdx.x;
   if (row_start * kTile >= n || col_group * kColTiles * kTile >= n) return;
   if (row_start > col_group * kColTiles + kColTiles - 1) return;
   mask_tiles<BoxT>(n, thr, boxes + o, smode[s] == 2 ? cls + o : nullptr, mask + moff[s], row_start, col_group,
-                   blk ? blk + roff[s] : nullptr);
+                   blk ? blk + roff[s] : nullptr, jmax ? jmax + roff[s] : nullptr, jmax ? wbase + roff[s] : nullptr);
 }
 
 // ---- 5. greedy scan -----------------------------------------------------------
@@ -524,15 +543,14 @@ __device__ __forceinline__ u64 resolve_block_warp(u64 alive, u64 d0, u64 d1, int
 // a warp combined by shuffles 1000 (the groups' row segments are 16 * stride words apart: 4-way bank conflicts).
 constexpr int kRowGroups = 4, kGroupRows = kTile / kRowGroups;
 
-__device__ __forceinline__ void or_rows(const u64* __restrict__ rowsb, u64* remv, u64 kept, int j0, int col_blocks,
-                                        int warp, int lane, int b) {
-  constexpr int kWorkers = kSmemThreads / 32 - 1;
-  const int stride = col_blocks - b;  // staged rows start at column block b
-  const int units = ((col_blocks - j0 + 31) / 32) * kRowGroups;
+__device__ __forceinline__ void or_rows(const u64* __restrict__ rowsb, u64* remv, u64 kept, int j0, int jend,
+                                        int col_blocks, int stride, int warp, int lane, int b) {
+  constexpr int kWorkers = kSmemThreads / 32 - 1;  // staged rows start at column block b, `stride` words apart
+  const int units = ((jend - j0 + 31) / 32) * kRowGroups;
   for (int u = warp - 1; u < units; u += kWorkers) {  // warp-uniform
     const int g = u % kRowGroups, j = j0 + (u / kRowGroups) * 32 + lane;
     const unsigned kq = (unsigned)(kept >> (kGroupRows * g)) & ((1u << kGroupRows) - 1u);
-    if (!kq || j >= col_blocks) continue;
+    if (!kq || j >= jend) continue;
     const u64* col = rowsb + (size_t)(kGroupRows * g) * stride + (j - b);
     u64 acc = 0;
 #pragma unroll
@@ -547,7 +565,9 @@ __device__ __forceinline__ void or_rows(const u64* __restrict__ rowsb, u64* remv
 __device__ __forceinline__ void scan_smem_body(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
     int64_t* __restrict__ keep, int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n,
-    const int32_t* __restrict__ rank = nullptr) {
+    const int32_t* __restrict__ rank = nullptr, const int32_t* __restrict__ jmax = nullptr,
+    const int32_t* __restrict__ wbase = nullptr) {
+  const MaskIdx mi{jmax, wbase, col_blocks};
   extern __shared__ __align__(16) u64 smem[];
   u64* remv = smem;                                    // [kRowGroups][col_blocks] partial words, OR = removed
   u64* keptw = smem + kRowGroups * col_blocks;         // [col_blocks]
@@ -572,19 +592,19 @@ __device__ __forceinline__ void scan_smem_body(
   // per copy, 3900 cycles per block.)
   auto prefetch_rows = [&](int b) {  // one thread
     if (b + 1 >= col_blocks) return;
-    const unsigned bytes = (unsigned)(kTile * (col_blocks - b) * sizeof(u64));
+    const unsigned bytes = (unsigned)(kTile * mi.width(b) * sizeof(u64));
     const unsigned bar = smem_u32(&s_bar[b & 1]);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic reads of this stage are done
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(stage + (size_t)(b & 1) * kTile * col_blocks)),
-                   "l"(mask + tri_base(b, col_blocks)), "r"(bytes), "r"(bar) : "memory");
+                   "l"(mask + mi.base(b)), "r"(bytes), "r"(bar) : "memory");
   };
   auto prefetch_diag = [&](int b, int i) {  // mask[b*64 + i][b], i < rows
     if (b >= col_blocks || i >= min(n - b * kTile, kTile)) return;
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;"
                  ::"r"(smem_u32(ring + (b & (kDiagRing - 1)) * kTile + i)),
-                   "l"(mask + tri_word(b, i, b, col_blocks)) : "memory");
+                   "l"(mask + mi.word(b, i, b)) : "memory");
   };
   auto resolve = [&](int b, u64 removed) {  // warp 0, all lanes
     const int rows = min(n - b * kTile, kTile);
@@ -623,12 +643,17 @@ __device__ __forceinline__ void scan_smem_body(
     SCAN_T(2)
     const u64 kept = keptw[b];
     const u64* rowsb = stage + (size_t)(b & 1) * kTile * col_blocks;
+    // class-grouped sets: words right of the block's last live tile were never written and are never read
+    const int jend = jmax ? min(col_blocks, jmax[b] + 1) : col_blocks;
+    const int stride = jend - b;  // row stride of the staged block = mi.width(b)
     if (warp == 0) {
       if (b + 1 < col_blocks) {
         // word b+1 of the kept rows of block b: two rows per lane, OR across the warp
         u64 v = 0;
-        if ((kept >> lane) & 1ULL) v |= rowsb[(size_t)lane * (col_blocks - b) + 1];
-        if ((kept >> (lane + 32)) & 1ULL) v |= rowsb[(size_t)(lane + 32) * (col_blocks - b) + 1];
+        if (b + 1 < jend) {
+          if ((kept >> lane) & 1ULL) v |= rowsb[(size_t)lane * stride + 1];
+          if ((kept >> (lane + 32)) & 1ULL) v |= rowsb[(size_t)(lane + 32) * stride + 1];
+        }
         if (lane < kRowGroups) v |= remv[lane * col_blocks + b + 1];  // the partial words of that column
         const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v);
         const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
@@ -637,8 +662,8 @@ __device__ __forceinline__ void scan_smem_body(
         if (lane == 0) keptw[b + 1] = k1;
         SCAN_T(4)
       }
-    } else if (kept && b + 2 < col_blocks) {
-      or_rows(rowsb, remv, kept, b + 2, col_blocks, warp, lane, b);
+    } else if (kept && b + 2 < jend) {
+      or_rows(rowsb, remv, kept, b + 2, jend, col_blocks, stride, warp, lane, b);
     }
     if (warp != 0) { SCAN_T(3) }
   }
@@ -661,17 +686,20 @@ __global__ void __launch_bounds__(kSmemThreads) nms_seg_scan_smem_kernel(
     const u64* __restrict__ mask, const int32_t* __restrict__ off, const long long* __restrict__ moff,
     const int32_t* __restrict__ roff, const int32_t* __restrict__ order, int64_t* __restrict__ keep,
     int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n,
-    const int32_t* __restrict__ rank) {
+    const int32_t* __restrict__ rank, const int32_t* __restrict__ jmax, const int32_t* __restrict__ wbase) {
   const int s = blockIdx.x;
   const int o = off[s], n = off[s + 1] - o;
   scan_smem_body(mask + moff[s], n, (n + kTile - 1) / kTile, order + o, keep + o, num_keep + s,
-                 init_remv + roff[s], top_n, rank ? rank + o : nullptr);
+                 init_remv + roff[s], top_n, rank ? rank + o : nullptr, jmax ? jmax + roff[s] : nullptr,
+                 jmax ? wbase + roff[s] : nullptr);
 }
 
 __device__ __forceinline__ void scan_body(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
     int64_t* __restrict__ keep, int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n,
-    const int32_t* __restrict__ rank = nullptr) {
+    const int32_t* __restrict__ rank = nullptr, const int32_t* __restrict__ jmax = nullptr,
+    const int32_t* __restrict__ wbase = nullptr) {
+  const MaskIdx mi{jmax, wbase, col_blocks};
   extern __shared__ u64 smem[];
   u64* remv = smem;                 // [col_blocks]
   u64* keptw = smem + col_blocks;   // [col_blocks]
@@ -684,7 +712,7 @@ __device__ __forceinline__ void scan_body(
 
   for (int b = 0; b < col_blocks; ++b) {
     const int rows = min(n - b * kTile, kTile);
-    if (tid < kTile) diag[tid] = tid < rows ? mask[tri_word(b, tid, b, col_blocks)] : 0ULL;
+    if (tid < kTile) diag[tid] = tid < rows ? mask[mi.word(b, tid, b)] : 0ULL;
     __syncthreads();
     if (tid == 0) {
       u64 alive = ~remv[b];
@@ -695,13 +723,14 @@ __device__ __forceinline__ void scan_body(
     }
     __syncthreads();
     const u64 kept = s_kept;
-    for (int j = b + 1 + tid; j < col_blocks; j += kScanThreads) {
+    const int jend = jmax ? min(col_blocks, jmax[b] + 1) : col_blocks;
+    for (int j = b + 1 + tid; j < jend; j += kScanThreads) {
       u64 acc = remv[j];
       u64 kk = kept;
       while (kk) {
         const int i = __ffsll((long long)kk) - 1;
         kk &= kk - 1;
-        acc |= mask[tri_word(b, i, j, col_blocks)];
+        acc |= mask[mi.word(b, i, j)];
       }
       remv[j] = acc;
     }
@@ -720,11 +749,11 @@ __global__ void __launch_bounds__(kScanThreads) nms_seg_scan_kernel(
     const u64* __restrict__ mask, const int32_t* __restrict__ off, const long long* __restrict__ moff,
     const int32_t* __restrict__ roff, const int32_t* __restrict__ order, int64_t* __restrict__ keep,
     int64_t* __restrict__ num_keep, const u64* __restrict__ init_remv, int top_n,
-    const int32_t* __restrict__ rank) {
+    const int32_t* __restrict__ rank, const int32_t* __restrict__ jmax, const int32_t* __restrict__ wbase) {
   const int s = blockIdx.x;
   const int o = off[s], n = off[s + 1] - o;
   scan_body(mask + moff[s], n, (n + kTile - 1) / kTile, order + o, keep + o, num_keep + s, init_remv + roff[s],
-            top_n, rank ? rank + o : nullptr);
+            top_n, rank ? rank + o : nullptr, jmax ? jmax + roff[s] : nullptr, jmax ? wbase + roff[s] : nullptr);
 }
 
 __global__ void nms_zero_count_kernel(int64_t* num_keep) { *num_keep = 0; }
@@ -996,6 +1025,59 @@ __global__ void nms_seg_blocks_kernel(const Box4f* __restrict__ sorted, const un
   }
 }
 
+// last live tile of every row block: jmax[b] = the largest column block j >= b whose tile (b, j) can hold a bit,
+// and wbase[b] = sum of the widths jmax - b + 1 of the blocks before b (the packed layout's block bases).
+// One CTA per segment; a warp finds jmax of a block by testing 32 column blocks at a time from the right.
+constexpr int kJmaxThreads = 256;
+__global__ void __launch_bounds__(kJmaxThreads) nms_seg_jmax_kernel(
+    const BlockSum* __restrict__ blk, const int32_t* __restrict__ roff, const int32_t* __restrict__ smode,
+    int skip_apart, int32_t* __restrict__ jmax, int32_t* __restrict__ wbase) {
+  const int s = blockIdx.x;
+  const int cb = roff[s + 1] - roff[s];
+  const BlockSum* sb = blk + roff[s];
+  int32_t* jm = jmax + roff[s];
+  int32_t* wb = wbase + roff[s];
+  const bool by_class = smode[s] == 2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int b = warp; b < cb; b += kJmaxThreads / 32) {
+    const BlockSum r = sb[b];
+    int found = b;
+    for (int hi = cb - 1; hi > b; hi -= 32) {  // columns hi - 31 .. hi
+      const int j = hi - lane;
+      const bool live = j > b && !tile_is_empty(r, sb[j], skip_apart != 0, by_class);
+      const unsigned m = __ballot_sync(0xffffffffu, live);
+      if (m) {
+        found = hi - (__ffs(m) - 1);
+        break;
+      }
+    }
+    if (lane == 0) jm[b] = found;
+  }
+  __syncthreads();
+  // exclusive prefix sum of the widths, a chunk of kJmaxThreads blocks at a time
+  __shared__ int s_warp[kJmaxThreads / 32];
+  __shared__ int s_carry;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int b0 = 0; b0 < cb; b0 += kJmaxThreads) {
+    const int b = b0 + threadIdx.x;
+    const int w = b < cb ? jm[b] - b + 1 : 0;
+    int incl = w;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int before = s_carry;
+    for (int k = 0; k < warp; ++k) before += s_warp[k];
+    if (b < cb) wb[b] = before + incl - w;
+    __syncthreads();
+    if (threadIdx.x == kJmaxThreads - 1) s_carry = before + incl;
+    __syncthreads();
+  }
+}
+
 // boxes into (segment, score) order; mode as nms_gather_kernel; filtered boxes start out removed
 template <typename T>
 __global__ void nms_seg_gather_kernel(const T* __restrict__ boxes, const int64_t* __restrict__ idxs,
@@ -1035,7 +1117,7 @@ __global__ void nms_seg_gather_kernel(const T* __restrict__ boxes, const int64_t
 
 struct SegLayout {
   u64 *keys_in, *keys_out, *mask, *init_remv;
-  int32_t *idx_in, *order, *cls, *off, *roff, *smode, *pos, *rank, *sgroup;
+  int32_t *idx_in, *order, *cls, *off, *roff, *smode, *pos, *rank, *sgroup, *jmax, *wbase;
   unsigned* ckey;
   BlockSum* blk;
   long long* moff;
@@ -1064,6 +1146,8 @@ SegLayout seg_carve(void* ws, long long n, long long S, long long mask_words, lo
   L.rank = (int32_t*)c.take(n * 4);
   L.ckey = (unsigned*)c.take(n * 4);
   L.blk = (BlockSum*)c.take((remv_words + 1) * sizeof(BlockSum));
+  L.jmax = (int32_t*)c.take((remv_words + 1) * 4);
+  L.wbase = (int32_t*)c.take((remv_words + 1) * 4);
   L.off = (int32_t*)c.take((S + 1) * 4);
   L.roff = (int32_t*)c.take((S + 1) * 4);
   L.smode = (int32_t*)c.take((S + 1) * 4);
@@ -1158,25 +1242,28 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
     const int warps = (int)remv_words;
     nms_seg_blocks_kernel<<<(warps * 32 + th - 1) / th, th, 0, st>>>(L.sorted, L.ckey, L.off, L.roff, (int)S, warps,
                                                                     L.blk);
+    nms_seg_jmax_kernel<<<(unsigned)S, kJmaxThreads, 0, st>>>(L.blk, L.roff, L.smode, (float)thr >= 0.f ? 1 : 0, L.jmax,
+                                                              L.wbase);
   }
   const int32_t* rank = grouped ? L.rank : nullptr;
+  const int32_t* jmax = grouped ? L.jmax : nullptr;
   if (cb_max > 0) {
     dim3 grid((cb_max + kColTiles - 1) / kColTiles, cb_max, (unsigned)S);
     nms_seg_mask_kernel<Box4f><<<grid, kTile, 0, st>>>(L.off, L.moff, L.smode, (float)thr, L.sorted, L.cls, L.mask,
-                                                       L.roff, grouped ? L.blk : nullptr);
+                                                       L.roff, grouped ? L.blk : nullptr, jmax, L.wbase);
   }
   if (cb_max <= kSmemBlocks) {
     const size_t smem = ((size_t)(kRowGroups + 1) * cb_max + 1 + kDiagRing * kTile + (size_t)2 * kTile * cb_max) * sizeof(u64) + 16;
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_seg_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     nms_seg_scan_smem_kernel<<<(unsigned)S, kSmemThreads, smem, st>>>(L.mask, L.off, L.moff, L.roff, L.order, keep,
-                                                                      counts, L.init_remv, top_n, rank);
+                                                                      counts, L.init_remv, top_n, rank, jmax, L.wbase);
   } else {
     const size_t smem = (size_t)cb_max * 16 + 16;
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_seg_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     nms_seg_scan_kernel<<<(unsigned)S, kScanThreads, smem, st>>>(L.mask, L.off, L.moff, L.roff, L.order, keep, counts,
-                                                                 L.init_remv, top_n, rank);
+                                                                 L.init_remv, top_n, rank, jmax, L.wbase);
   }
   B200DET_CUDA_OK(cudaGetLastError());
   return 0;
