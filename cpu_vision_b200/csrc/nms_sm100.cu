@@ -259,36 +259,64 @@ __device__ __forceinline__ float box_area(const Box4f& b) {
   return __fmul_rn(__fsub_rn(b.x2, b.x1), __fsub_rn(b.y2, b.y1));
 }
 
+// packed pairs of fp32 (FADD2 / FMUL2 / FFMA2 on sm_100): each half is the IEEE .rn operation
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void upk2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+
+// column boxes of a tile, one array per field so that two neighbouring columns load as one packed pair
+struct ColTile { float x1[kTile], y1[kTile], x2[kTile], y2[kTile], area[kTile]; };
+
+// Two columns per step: min / max stay scalar (no packed form), the subtractions, products and the fma run packed.
 template <bool HAS_CLS>
-__device__ __forceinline__ u64 tile_bits_f32(const Box4f& a, float sa, int32_t ac, const Box4f* __restrict__ cb,
-                                             const float* __restrict__ carea, const int32_t* __restrict__ cc,
-                                             float thr, u64 valid) {
+__device__ __forceinline__ u64 tile_bits_f32(const Box4f& a, float sa, int32_t ac, const ColTile& c,
+                                             const int32_t* __restrict__ cc, float thr, u64 valid) {
   unsigned w[2] = {0u, 0u}, u[2] = {0u, 0u};
+  const f32x2 sa2 = pk2(sa, sa), nthr2 = pk2(-thr, -thr), eps2 = pk2(kSureMargin, kSureMargin);
 #pragma unroll
-  for (int i = 0; i < kTile; ++i) {
-    const Box4f b = cb[i];
-    const float left = fmaxf(a.x1, b.x1), right = fminf(a.x2, b.x2);
-    const float top = fmaxf(a.y1, b.y1), bottom = fminf(a.y2, b.y2);
-    const float iw = fmaxf(__fsub_rn(right, left), 0.f), ih = fmaxf(__fsub_rn(bottom, top), 0.f);
-    const float inter = __fmul_rn(iw, ih);
-    const float uni = __fsub_rn(__fadd_rn(sa, carea[i]), inter);
-    const float r = __fmaf_rn(-thr, uni, inter);
-    bool sure = (uni > 0.f) && (fabsf(r) > __fmul_rn(uni, kSureMargin));
-    bool hit = sure && (r > 0.f);
+  for (int i = 0; i < kTile; i += 2) {
+    const float2 bx1 = *reinterpret_cast<const float2*>(&c.x1[i]), by1 = *reinterpret_cast<const float2*>(&c.y1[i]);
+    const float2 bx2 = *reinterpret_cast<const float2*>(&c.x2[i]), by2 = *reinterpret_cast<const float2*>(&c.y2[i]);
+    const f32x2 sb2 = *reinterpret_cast<const f32x2*>(&c.area[i]);
+    const f32x2 left = pk2(fmaxf(a.x1, bx1.x), fmaxf(a.x1, bx1.y)), right = pk2(fminf(a.x2, bx2.x), fminf(a.x2, bx2.y));
+    const f32x2 top = pk2(fmaxf(a.y1, by1.x), fmaxf(a.y1, by1.y)), bottom = pk2(fminf(a.y2, by2.x), fminf(a.y2, by2.y));
+    float w0, w1, h0, h1;
+    upk2(sub2(right, left), w0, w1);
+    upk2(sub2(bottom, top), h0, h1);
+    const f32x2 inter = mul2(pk2(fmaxf(w0, 0.f), fmaxf(w1, 0.f)), pk2(fmaxf(h0, 0.f), fmaxf(h1, 0.f)));
+    const f32x2 uni = sub2(add2(sa2, sb2), inter);
+    float r0, r1, m0, m1, u0, u1;
+    upk2(fma2(nthr2, uni, inter), r0, r1);
+    upk2(mul2(uni, eps2), m0, m1);
+    upk2(uni, u0, u1);
+    bool sure0 = (u0 > 0.f) && (fabsf(r0) > m0), sure1 = (u1 > 0.f) && (fabsf(r1) > m1);
+    bool hit0 = sure0 && (r0 > 0.f), hit1 = sure1 && (r1 > 0.f);
     if (HAS_CLS) {
-      const bool same = cc[i] == ac;
-      hit = hit && same;
-      sure = sure || !same;
+      const bool same0 = cc[i] == ac, same1 = cc[i + 1] == ac;
+      hit0 = hit0 && same0; sure0 = sure0 || !same0;
+      hit1 = hit1 && same1; sure1 = sure1 || !same1;
     }
-    if (hit) w[i >> 5] |= 1u << (i & 31);
-    if (!sure) u[i >> 5] |= 1u << (i & 31);
+    if (hit0) w[i >> 5] |= 1u << (i & 31);
+    if (hit1) w[i >> 5] |= 2u << (i & 31);
+    if (!sure0) u[i >> 5] |= 1u << (i & 31);
+    if (!sure1) u[i >> 5] |= 2u << (i & 31);
   }
   u64 bits = (((u64)w[1] << 32) | w[0]) & valid;
   u64 open = (((u64)u[1] << 32) | u[0]) & valid;
   while (open) {  // rare: the exact quotient decides
     const int i = __ffsll((long long)open) - 1;
     open &= open - 1;
-    if (iou_gt(a, cb[i], thr)) bits |= 1ULL << i;
+    Box4f b;
+    b.x1 = c.x1[i]; b.y1 = c.y1[i]; b.x2 = c.x2[i]; b.y2 = c.y2[i];
+    if (iou_gt(a, b, thr)) bits |= 1ULL << i;
   }
   return bits;
 }
@@ -315,7 +343,7 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
   const int row_size = min(n - row_start * kTile, kTile);
   __shared__ BoxT cb[kTile];
   __shared__ int32_t cc[kTile];
-  __shared__ float carea[kTile];
+  __shared__ __align__(16) ColTile ct;  // fp32 fast path only
   const int cur = kTile * row_start + threadIdx.x;
   const bool have_row = (int)threadIdx.x < row_size;
   BoxT a = boxes[have_row ? cur : kTile * row_start];
@@ -340,7 +368,11 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
       const BoxT b = boxes[kTile * col_start + threadIdx.x];
       cb[threadIdx.x] = b;
       cc[threadIdx.x] = cls ? cls[kTile * col_start + threadIdx.x] : 0;
-      if constexpr (kF32) carea[threadIdx.x] = box_area(b);
+      if constexpr (kF32) {
+        ct.x1[threadIdx.x] = b.x1; ct.y1[threadIdx.x] = b.y1;
+        ct.x2[threadIdx.x] = b.x2; ct.y2[threadIdx.x] = b.y2;
+        ct.area[threadIdx.x] = box_area(b);
+      }
     }
     __syncthreads();
     if (!have_row) continue;
@@ -351,8 +383,8 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
         // entries past col_size hold stale boxes; their bits are masked off, like those up to the diagonal
         u64 valid = col_size == kTile ? ~0ULL : ((1ULL << col_size) - 1ULL);
         valid &= start >= kTile ? 0ULL : (~0ULL << start);
-        w = cls ? tile_bits_f32<true>(a, sa, ac, cb, carea, cc, thr, valid)
-                : tile_bits_f32<false>(a, sa, ac, cb, carea, cc, thr, valid);
+        w = cls ? tile_bits_f32<true>(a, sa, ac, ct, cc, thr, valid)
+                : tile_bits_f32<false>(a, sa, ac, ct, cc, thr, valid);
         mask[mi.word(row_start, threadIdx.x, col_start)] = w;
         continue;
       }
