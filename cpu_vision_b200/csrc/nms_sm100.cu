@@ -272,13 +272,17 @@ __device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 d; asm("sub.rn.f
 __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
 
+__device__ __forceinline__ bool box_is_proper(const Box4f& b, float area) {
+  return b.x2 >= b.x1 && b.y2 >= b.y1 && area > 0.f && area < INFINITY;
+}
+
 // column boxes of a tile, one array per field so that two neighbouring columns load as one packed pair
 struct ColTile { float x1[kTile], y1[kTile], x2[kTile], y2[kTile], area[kTile]; };
 
 // Two columns per step: min / max stay scalar (no packed form), the subtractions, products and the fma run packed.
 template <bool HAS_CLS>
 __device__ __forceinline__ u64 tile_bits_f32(const Box4f& a, float sa, int32_t ac, const ColTile& c,
-                                             const int32_t* __restrict__ cc, float thr, u64 valid) {
+                                             const int32_t* __restrict__ cc, float thr, u64 valid, u64 improper) {
   unsigned w[2] = {0u, 0u}, u[2] = {0u, 0u};
   const f32x2 sa2 = pk2(sa, sa), nthr2 = pk2(-thr, -thr), eps2 = pk2(kSureMargin, kSureMargin);
 #pragma unroll
@@ -293,11 +297,12 @@ __device__ __forceinline__ u64 tile_bits_f32(const Box4f& a, float sa, int32_t a
     upk2(sub2(bottom, top), h0, h1);
     const f32x2 inter = mul2(pk2(fmaxf(w0, 0.f), fmaxf(w1, 0.f)), pk2(fmaxf(h0, 0.f), fmaxf(h1, 0.f)));
     const f32x2 uni = sub2(add2(sa2, sb2), inter);
-    float r0, r1, m0, m1, u0, u1;
+    float r0, r1, m0, m1;
     upk2(fma2(nthr2, uni, inter), r0, r1);
     upk2(mul2(uni, eps2), m0, m1);
-    upk2(uni, u0, u1);
-    bool sure0 = (u0 > 0.f) && (fabsf(r0) > m0), sure1 = (u1 > 0.f) && (fabsf(r1) > m1);
+    // union > 0 is guaranteed for proper boxes (x2 >= x1, y2 >= y1, finite area > 0: inter <= min(Sa, Sb), so
+    // (Sa + Sb) - inter >= inter (1 - 2^-23) and > 0); improper rows / columns are sent to the exact path by `valid_fast`
+    bool sure0 = fabsf(r0) > m0, sure1 = fabsf(r1) > m1;
     bool hit0 = sure0 && (r0 > 0.f), hit1 = sure1 && (r1 > 0.f);
     if (HAS_CLS) {
       const bool same0 = cc[i] == ac, same1 = cc[i + 1] == ac;
@@ -309,8 +314,14 @@ __device__ __forceinline__ u64 tile_bits_f32(const Box4f& a, float sa, int32_t a
     if (!sure0) u[i >> 5] |= 1u << (i & 31);
     if (!sure1) u[i >> 5] |= 2u << (i & 31);
   }
-  u64 bits = (((u64)w[1] << 32) | w[0]) & valid;
-  u64 open = (((u64)u[1] << 32) | u[0]) & valid;
+  u64 bits = (((u64)w[1] << 32) | w[0]) & valid & ~improper;
+  u64 open = ((((u64)u[1] << 32) | u[0]) | improper) & valid;
+  if (HAS_CLS) {  // an improper column of another class cannot set a bit
+    for (u64 m = improper & valid; m; m &= m - 1) {
+      const int i = __ffsll((long long)m) - 1;
+      if (cc[i] != ac) open &= ~(1ULL << i);
+    }
+  }
   while (open) {  // rare: the exact quotient decides
     const int i = __ffsll((long long)open) - 1;
     open &= open - 1;
@@ -344,6 +355,7 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
   __shared__ BoxT cb[kTile];
   __shared__ int32_t cc[kTile];
   __shared__ __align__(16) ColTile ct;  // fp32 fast path only
+  __shared__ unsigned s_improper[2];    // columns of the tile that must take the exact division
   const int cur = kTile * row_start + threadIdx.x;
   const bool have_row = (int)threadIdx.x < row_size;
   BoxT a = boxes[have_row ? cur : kTile * row_start];
@@ -352,7 +364,11 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
   constexpr bool kF32 = std::is_same<BoxT, Box4f>::value;
   const bool fast = kF32 && thr >= 9.5367431640625e-07f && thr <= 1.f;
   float sa = 0.f;
-  if constexpr (kF32) sa = box_area(a);
+  bool row_improper = false;
+  if constexpr (kF32) {
+    sa = box_area(a);
+    row_improper = !box_is_proper(a, sa);
+  }
   for (int t = 0; t < kColTiles; ++t) {
     const int col_start = col_group * kColTiles + t;
     if (col_start >= col_blocks) break;
@@ -364,15 +380,22 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
       continue;
     }
     __syncthreads();  // the previous tile's columns are no longer read
+    bool col_improper = false;
     if ((int)threadIdx.x < col_size) {
       const BoxT b = boxes[kTile * col_start + threadIdx.x];
       cb[threadIdx.x] = b;
       cc[threadIdx.x] = cls ? cls[kTile * col_start + threadIdx.x] : 0;
       if constexpr (kF32) {
+        const float area = box_area(b);
         ct.x1[threadIdx.x] = b.x1; ct.y1[threadIdx.x] = b.y1;
         ct.x2[threadIdx.x] = b.x2; ct.y2[threadIdx.x] = b.y2;
-        ct.area[threadIdx.x] = box_area(b);
+        ct.area[threadIdx.x] = area;
+        col_improper = !box_is_proper(b, area);
       }
+    }
+    if constexpr (kF32) {
+      const unsigned m = __ballot_sync(0xffffffffu, col_improper);
+      if ((threadIdx.x & 31) == 0) s_improper[threadIdx.x >> 5] = m;
     }
     __syncthreads();
     if (!have_row) continue;
@@ -383,8 +406,9 @@ __device__ __forceinline__ void mask_tiles(int n, float thr, const BoxT* __restr
         // entries past col_size hold stale boxes; their bits are masked off, like those up to the diagonal
         u64 valid = col_size == kTile ? ~0ULL : ((1ULL << col_size) - 1ULL);
         valid &= start >= kTile ? 0ULL : (~0ULL << start);
-        w = cls ? tile_bits_f32<true>(a, sa, ac, ct, cc, thr, valid)
-                : tile_bits_f32<false>(a, sa, ac, ct, cc, thr, valid);
+        const u64 improper = row_improper ? ~0ULL : (((u64)s_improper[1] << 32) | s_improper[0]);
+        w = cls ? tile_bits_f32<true>(a, sa, ac, ct, cc, thr, valid, improper)
+                : tile_bits_f32<false>(a, sa, ac, ct, cc, thr, valid, improper);
         mask[mi.word(row_start, threadIdx.x, col_start)] = w;
         continue;
       }
