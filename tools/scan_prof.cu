@@ -1,4 +1,6 @@
-// Where does the single-CTA NMS scan spend its cycles?  Build: nvcc -DB200DET_SCAN_PROFILE ... (see tools/scan_prof.sh)
+// Where does the single-CTA NMS scan spend its cycles?  clock64() counters per phase of scan_smem_body.
+// Build: nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -DB200DET_SCAN_PROFILE \
+//          -o tools/bin/scan_prof tools/scan_prof.cu      (tools/bin/ is git-ignored; run it under gpurun)
 #include "../cpu_vision_b200/csrc/nms_sm100.cu"
 #include <cstdio>
 #include <vector>
