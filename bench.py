@@ -500,6 +500,24 @@ def secondary_legs(capi, dev, peak):
                    flush_l2=False)
     det_n = sum(b_.shape[0] for b_ in detection.postprocess_detections(lg, rg, rp, shapes, 0.05, 0.5, 100)[0])
     del rp, lg, rg
+    # cfg3 in bf16 (BASELINE.json configs[2] names fp32 and bf16): same kernels, 2-byte elements, packed
+    # red.global.add.v4.bf16x2 in the backward; the working set (1.41 GB) exceeds L2, no flush
+    fb_, rb_, gb_ = make_cfg3(dev, torch.bfloat16, 1239)
+    Kb = rb_.shape[0]
+    ob_ = torch.empty(Kb, C, 14, 14, device=dev, dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    gfb_ = [torch.empty_like(f) for f in fb_]
+    _, lvb_ = capi.msroi_align_forward(fb_, rb_, SCALES, 14, 14, 2, False, out=ob_)
+    shp_ = [(16, C, h, w) for h, w in SHAPES]
+    bf_f = timed(lambda: capi.msroi_align_forward(fb_, rb_, SCALES, 14, 14, 2, False, out=ob_), iters=10, flush_l2=False)
+    bf_b = timed(lambda: capi.msroi_align_backward(gb_, rb_, lvb_, SCALES, shp_, 14, 14, 2, False, layout=capi.NHWC,
+                                                   outs=gfb_), iters=10, flush_l2=False)
+    bytes_b = sum(f.numel() for f in fb_) * 2 + gb_.numel() * 2 + Kb * 24
+    res["cfg3_bf16"] = {
+        "fwd_ms": bf_f, "bwd_ms": bf_b, "fwd_bwd_rois_per_s": Kb / ((bf_f + bf_b) / 1e3),
+        "algorithmic_bytes_per_launch": bytes_b, "fwd_frac_of_hbm": bytes_b / (bf_f / 1e3) / 1e9 / peak,
+        "bwd_frac_of_hbm": bytes_b / (bf_b / 1e3) / 1e9 / peak,
+        "note": "parity within 1e-2 of the fp32 oracle (tests/test_roi_align_gpu.py); also selectable as --workload cfg3_bf16"}
+    del fb_, rb_, gb_, ob_, gfb_
     # cfg3 as an NCHW caller sees it (the reference's models hand NCHW-contiguous features to roi_align):
     # the dispatcher shim re-lays out -> channels_last kernels -> re-lays out; results are NCHW-contiguous
     import cpu_vision_b200  # noqa: F401
