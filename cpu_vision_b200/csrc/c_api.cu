@@ -97,6 +97,12 @@ static int backward_impl(const LevelArgs& lv, int dtype, const void* grad, const
     int taken = 0;
     int rc = 0;
     static const bool tile_env = getenv("B200DET_BWD_TILE") && atoi(getenv("B200DET_BWD_TILE")) != 0;
+    static const int strip_env = getenv("B200DET_BWD_STRIP") ? atoi(getenv("B200DET_BWD_STRIP")) : -1;
+    if (strip_env == 1 || (deterministic && !tile_env)) {  // write-once strips: no atomics, fixed order
+      rc = roi_align_bwd_strip(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
+                               zero_init, st, &taken);
+      if (rc != 0 || taken) return rc;
+    }
     if (deterministic || tile_env) {  // tile accumulation: every byte written once, fixed order
       rc = roi_align_bwd_tile(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
                               zero_init, st, &taken);

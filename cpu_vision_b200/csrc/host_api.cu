@@ -420,6 +420,7 @@ void b200det_host_release(void) {
   std::lock_guard<std::mutex> lock(g_mu);
   roi_align_bwd_release();
   roi_align_bwd_tile_release();
+  roi_align_bwd_strip_release();
   if (g_arena.device < 0) return;
   cudaSetDevice(g_arena.device);
   for (int i = 0; i < 6; ++i) {

@@ -46,6 +46,12 @@ int roi_align_bwd_tile(const LevelArgs& lv, int dtype, const void* grad, const i
                        const void* rois, const int32_t* levels, long long K, int PH, int PW,
                        int sr, bool aligned, bool zero_init, cudaStream_t st, int* taken);
 void roi_align_bwd_tile_release();
+// roi_align_bwd_strip_sm100.cu: write-once backward (a warp owns a strip of one feature row; shared-memory
+// accumulators, no atomics, no memset, deterministic); same contract
+int roi_align_bwd_strip(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
+                        const void* rois, const int32_t* levels, long long K, int PH, int PW,
+                        int sr, bool aligned, bool zero_init, cudaStream_t st, int* taken);
+void roi_align_bwd_strip_release();
 
 // nms_sm100.cu
 size_t nms_workspace_bytes(long long N);
