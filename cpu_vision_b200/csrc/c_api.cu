@@ -96,26 +96,41 @@ static int backward_impl(const LevelArgs& lv, int dtype, const void* grad, const
     if (!rois || !grad || !gs) return fail(B200DET_EINVAL, "roi_align backward: null pointer");
     int taken = 0;
     int rc = 0;
-    static const bool tile_env = getenv("B200DET_BWD_TILE") && atoi(getenv("B200DET_BWD_TILE")) != 0;
+    // Which kernel produces which level.  The write-once strip kernel (shared-memory accumulators, every
+    // gradient byte stored once, deterministic) takes the levels whose maps are too big for L2 to act as the
+    // accumulator: there a red costs a zero fill, a DRAM read-modify-write and a write-back per line.  The
+    // vector-red scatter takes the rest (dense, L2-resident coarse levels).  B200DET_BWD_STRIP=1 / 0 forces
+    // everything / nothing onto the strips; the deterministic flag means strips for every level.
     static const int strip_env = getenv("B200DET_BWD_STRIP") ? atoi(getenv("B200DET_BWD_STRIP")) : -1;
-    if (strip_env == 1 || (deterministic && !tile_env)) {  // write-once strips: no atomics, fixed order
-      rc = roi_align_bwd_strip(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
-                               zero_init, st, &taken);
-      if (rc != 0 || taken) return rc;
+    static const double strip_min_mb = getenv("B200DET_STRIP_MIN_MB") ? atof(getenv("B200DET_STRIP_MIN_MB")) : 1e30;
+    const unsigned all_levels = (1u << lv.num_levels) - 1u;
+    unsigned strip_levels = 0;
+    if (deterministic || strip_env == 1) {
+      strip_levels = all_levels;
+    } else if (strip_env < 0) {
+      for (int l = 0; l < lv.num_levels; ++l) {
+        const double mb = (double)lv.batch * lv.channels * lv.height[l] * lv.width[l] * dtype_size(dtype) / 1048576.0;
+        if (mb >= strip_min_mb) strip_levels |= 1u << l;
+      }
     }
-    if (deterministic || tile_env) {  // tile accumulation: every byte written once, fixed order
-      rc = roi_align_bwd_tile(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
-                              zero_init, st, &taken);
-      if (rc != 0 || taken) return rc;
-      if (deterministic)
+    unsigned done_levels = 0;
+    if (strip_levels) {
+      rc = roi_align_bwd_strip(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0, zero_init,
+                               strip_levels, st, &taken);
+      if (rc != 0) return rc;
+      if (taken) done_levels = strip_levels;
+      else if (deterministic)
         return fail(B200DET_ENOSUP,
                     "roi_align backward: the deterministic kernel needs channels_last tensors, C %% 128 == 0, "
                     "sampling_ratio 1 or 2 and a channel-contiguous gradient");
     }
-    // fused zero fill + vector-red scatter
-    rc = roi_align_bwd_fast(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0,
-                            zero_init, st, &taken);
+    if (done_levels == all_levels) return 0;
+    // fused zero fill + vector-red scatter for the remaining levels
+    rc = roi_align_bwd_fast(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0, zero_init,
+                            done_levels, st, &taken);
     if (rc != 0 || taken) return rc;
+    if (done_levels)
+      return fail(B200DET_ENOSUP, "roi_align backward: internal -- the scatter kernel refused a call the strip kernel took");
   }
   if (zero_init) {
     for (int l = 0; l < lv.num_levels; ++l) {

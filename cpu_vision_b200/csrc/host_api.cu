@@ -419,7 +419,6 @@ int b200det_batched_nms_host(const void* boxes, const void* scores, const int64_
 void b200det_host_release(void) {
   std::lock_guard<std::mutex> lock(g_mu);
   roi_align_bwd_release();
-  roi_align_bwd_tile_release();
   roi_align_bwd_strip_release();
   if (g_arena.device < 0) return;
   cudaSetDevice(g_arena.device);

@@ -36,21 +36,19 @@ int fpn_level_map(const void* rois, int dtype, long long K, int k_min, int k_max
 int roi_align_fwd_fast(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
                        void* out, int out_layout, long long K, int PH, int PW, int sr,
                        bool aligned, cudaStream_t st, int* taken);
-// The backward zero-fills the gradients itself when zero_init is set (fused with the scatter).
+// The backward zero-fills the gradients itself when zero_init is set (fused with the scatter).  Levels named in
+// skip_levels (bit l) are left alone: their RoIs are skipped and their maps not zero-filled (the strip kernel
+// produces them).
 int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
                        const void* rois, const int32_t* levels, long long K, int PH, int PW,
-                       int sr, bool aligned, bool zero_init, cudaStream_t st, int* taken);
+                       int sr, bool aligned, bool zero_init, unsigned skip_levels, cudaStream_t st, int* taken);
 void roi_align_bwd_release();
-// roi_align_bwd_tile_sm100.cu: tile-accumulating backward (no atomics, deterministic); same contract
-int roi_align_bwd_tile(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
-                       const void* rois, const int32_t* levels, long long K, int PH, int PW,
-                       int sr, bool aligned, bool zero_init, cudaStream_t st, int* taken);
-void roi_align_bwd_tile_release();
 // roi_align_bwd_strip_sm100.cu: write-once backward (a warp owns a strip of one feature row; shared-memory
-// accumulators, no atomics, no memset, deterministic); same contract
+// accumulators, no atomics, no memset, deterministic); produces the levels named in level_mask (bit l) and
+// leaves the others untouched
 int roi_align_bwd_strip(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
                         const void* rois, const int32_t* levels, long long K, int PH, int PW,
-                        int sr, bool aligned, bool zero_init, cudaStream_t st, int* taken);
+                        int sr, bool aligned, bool zero_init, unsigned level_mask, cudaStream_t st, int* taken);
 void roi_align_bwd_strip_release();
 
 // nms_sm100.cu

@@ -14,22 +14,17 @@
 // 16 bytes per lane, 512 B per warp instruction) instead of the reference's 4
 // scalar atomics per sample and channel (cuda/roi_align_kernel.cu:303-327).
 //
-// Memory system.  With a separate memset the reds of a 1.2 GB gradient miss L2:
-// every line is written as zeros, read back from HBM by the first red and
-// written again (ncu, r01: 61% of red sectors missed, +0.9 GB of reads).  So the
-// zero fill is FUSED and PHASED: RoIs arrive grouped by image (the reference's
-// convert_boxes_to_roi_format, ops/_utils.py:18-25, builds them that way); images
-// are cut into groups whose gradient fits in about half the L2; a persistent
-// grid works group by group: the zero chunks of group g+1 are interleaved, one
-// per finished task, with the scatter tasks of group g, and nobody starts
-// group g+1 before all of its chunks are written.  Reds then hit zero lines that
-// are still dirty in L2 and every gradient line goes to HBM once.  Progress needs
-// no co-residency: a warp only ever waits for chunks that running warps have
-// already claimed.  RoIs that are not grouped by image (a tiny plan kernel
-// checks) are handled as one group: still one launch, same results.
+// Memory system.  The zero fill is FUSED into the same persistent launch as a phase in front:
+// chunks of ~125 KB are claimed from a second counter and a warp scatters only after every chunk is
+// reported done (no co-residency assumption: a warp only ever waits for chunks that running warps have
+// already claimed).  A segmented schedule (RoIs counting-sorted by image / level / band of rows, fill just
+// in time) was measured in round 1 and lost (profiles/r01_bwd_rows_segments.md); it is gone.  Levels whose
+// map is too big and too sparsely covered for L2 to act as the accumulator are left to the write-once
+// strip kernel (roi_align_bwd_strip_sm100.cu): `skip_levels` names them, their RoIs are skipped here and
+// their maps are not zero-filled here.
 #include <stdlib.h>
 
-#include <vector>
+#include <mutex>
 
 #include "sm100_common.cuh"
 
@@ -38,38 +33,16 @@ namespace {
 
 constexpr int kBwdWarps = 4;
 constexpr int kMaxRows = 8;        // 2 pooled rows x 2 samples x 2 taps
-constexpr int kMaxSegs = 32;       // segments (level, band of rows) per image
-constexpr int kMaxGroups = 8192;   // images x segments a plan can index; more -> single group
 constexpr int kPlanSlots = 8;      // calls in flight on different streams before a slot is reused
 
-// A GROUP is one segment of one image: a band of rows of one level, i.e. one contiguous byte range of
-// the gradient, small enough that two of them sit in L2 together (B200DET_BWD_GROUP_MB).  A RoI
-// belongs to the group that holds the LAST feature row it taps; everything else it taps lies in
-// groups that come earlier in processing order, so it is already zero-filled.
-struct SegTable {
-  int nseg;                             // per image; 0: no segmentation (one group for everything)
-  int level[kMaxSegs], row0[kMaxSegs], rows[kMaxSegs];
-  int first_seg[B200DET_MAX_LEVELS], band_rows[B200DET_MAX_LEVELS], nbands[B200DET_MAX_LEVELS];
-  int zfirst[kMaxSegs + 1];             // zero chunks of an image before segment s; [nseg]: per image
-  // levels too big to keep in L2 between fill and scatter are zero-filled up front, all images at once
-  int up_mask;                          // bit l: level l is filled up front
-  int zup;                              // chunks of the up-front fill (numbered before all others)
-  int up_first[B200DET_MAX_LEVELS + 1]; // first up-front chunk of level l
-};
-
-// per-call scheduling state, followed in memory by gid[Kcap], order[Kcap], gsorted[Kcap]
+// per-call scheduling state; the three hot words sit in different 128-byte lines: 2368 warps hammer them
 struct BwdPlan {
-  // the three hot words sit in different 128-byte lines: 2368 warps hammer them
-  int task_ctr;                    // next scatter task (global, in group order)
+  int task_ctr;                    // next scatter task
   int pad0[31];
-  int zero_ctr;                    // next zero chunk (global, in group order)
+  int zero_ctr;                    // next zero chunk
   int pad1[31];
-  int up_done;                     // up-front chunks finished
+  int zero_done;                   // chunks finished
   int pad2[31];
-  int zero_done[kMaxGroups];       // per group: chunks finished
-  int count[kMaxGroups];           // RoIs of the group
-  int start[kMaxGroups + 8];       // exclusive scan of count
-  int cursor[kMaxGroups];          // fill positions of the counting sort
 };
 
 struct __align__(16) BYEnt { int rowoff; float w0; float w1; int pad; };
@@ -78,77 +51,6 @@ struct BwdWarpTables {
   XTab x;
   BYEnt y[kMaxRows];
 };
-
-// ---- plan: counting sort of the RoIs by group ----------------------------------------------
-// (1) group id of every RoI + histogram, (2) exclusive scan (one CTA), (3) fill order[].
-template <int SR>
-__global__ void bwd_plan_gid_kernel(LevelTable<float> lv, SegTable sg, const float* __restrict__ rois,
-                                    const int32_t* __restrict__ levels, int K, int N, int PH, int PW, bool aligned,
-                                    int* __restrict__ gid, BwdPlan* __restrict__ plan) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= K) return;
-  const int l = levels ? __ldg(levels + k) : 0;
-  const RoiGeom<float> g = roi_geometry<float>(rois + (long long)k * 5, lv.scale[l], PH, PW, SR, aligned);
-  int r_last = -1;
-  for (int s = 0; s < PH * SR; ++s) {
-    const AxisTap<float> t = axis_tap<float>(sample_coord<float>(g.start_h, g.bin_h, s / SR, s % SR, SR), lv.height[l]);
-    if (t.valid) r_last = max(r_last, t.hi);
-  }
-  int id = 0;  // RoIs that scatter nothing (bad image index, no valid sample) can sit anywhere
-  if ((unsigned)g.batch < (unsigned)N && r_last >= 0)
-    id = g.batch * sg.nseg + sg.first_seg[l] + min(r_last / sg.band_rows[l], sg.nbands[l] - 1);
-  gid[k] = id;
-  atomicAdd(&plan->count[id], 1);
-}
-
-__global__ void __launch_bounds__(1024) bwd_plan_scan_kernel(BwdPlan* __restrict__ plan, int G) {
-  __shared__ int wsum[32];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  constexpr int PER = kMaxGroups / 1024;
-  int v[PER], tot = 0;
-#pragma unroll
-  for (int i = 0; i < PER; ++i) {
-    const int g = tid * PER + i;
-    v[i] = g < G ? plan->count[g] : 0;
-    tot += v[i];
-  }
-  int incl = tot;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int t = __shfl_up_sync(kFull, incl, o);
-    if (lane >= o) incl += t;
-  }
-  if (lane == 31) wsum[warp] = incl;
-  __syncthreads();
-  if (warp == 0) {
-    int w = wsum[lane], wi = w;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(kFull, wi, o);
-      if (lane >= o) wi += t;
-    }
-    wsum[lane] = wi - w;
-  }
-  __syncthreads();
-  int run = wsum[warp] + incl - tot;
-#pragma unroll
-  for (int i = 0; i < PER; ++i) {
-    const int g = tid * PER + i;
-    if (g < G) { plan->start[g] = run; plan->cursor[g] = run; }
-    run += v[i];
-    if (g == G - 1) plan->start[G] = run;
-  }
-}
-
-__global__ void bwd_plan_fill_kernel(const int* __restrict__ gid, int K, BwdPlan* __restrict__ plan,
-                                     int* __restrict__ order, int* __restrict__ gsorted) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= K) return;
-  const int g = gid[k];
-  const int pos = atomicAdd(&plan->cursor[g], 1);
-  order[pos] = k;
-  gsorted[pos] = g;
-}
 
 // ---- y axis of a pair of pooled rows ----------------------------------------------------
 // Lane t < 4*SR computes one tap (pooled row 2*rp + t / (2*SR), sample, lo/hi); taps
@@ -482,72 +384,35 @@ struct BwdArgs {
   const int32_t* levels;
   const void* grad;
   long long gs_k, gs_c, gs_h, gs_w;
-  BwdPlan* plan;        // nullptr: one group, static task assignment, caller has zeroed
-  const int* order;     // RoIs sorted by group (segmented plans only)
-  const int* gsorted;   // group of order[p]
+  BwdPlan* plan;        // nullptr: static task assignment, the caller has zeroed
   int ztotal;           // zero chunks of the whole call; 0: no zero fill
-  int zlook, zper;      // the fill runs up to zlook groups ahead of the scatter, at most zper chunks per task
   long long K;
   int N, C, PH, PW, CT, RP;
-  int ngroups;          // 1: everything is one group
   int zero_chunk;       // bytes per zero chunk (multiple of 512); 0: no zero fill
+  unsigned skip_levels; // bit l: the RoIs of level l are not this launch's (another launch or the strip kernel has them)
+  unsigned nozero_levels;  // bit l: the map of level l is not zero-filled by this launch
   bool vec, aligned;
   int mode;             // 0: pooled-row pair sweep, 1: feature-row gather
-  SegTable sg;
 };
 
-// pacing reads need no ordering (and ld.acquire costs an L1 invalidation each time)
-__device__ __forceinline__ int ld_relaxed(const int* p) {
-  int v;
-  asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 __device__ __forceinline__ int ld_acquire(const int* p) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 
-template <typename T>
-__device__ __forceinline__ long long seg_bytes(const LevelTable<T>& lv, const BwdArgs& a, int seg) {
-  const int l = a.sg.level[seg];
-  return (long long)a.sg.rows[seg] * lv.sh[l] * (long long)sizeof(T);
-}
-
-// writes zero chunk z (global numbering, group order) and reports it done; all lanes participate
+// writes zero chunk z (levels in order, skipped levels have none) and reports it done; all lanes participate
 template <typename T>
 __device__ __forceinline__ void zero_chunk(const LevelTable<T>& lv, const BwdArgs& a, int z, int lane) {
   char* p = nullptr;
   long long bytes = 0;
-  int c = z, g = 0;
-  if (a.ngroups == 1) {
-    for (int l = 0; l < lv.num_levels; ++l) {
-      bytes = (long long)a.N * lv.sn[l] * (long long)sizeof(T);
-      const int n = (int)((bytes + a.zero_chunk - 1) / a.zero_chunk);
-      if (c < n) { p = reinterpret_cast<char*>(lv.ptr[l]); break; }
-      c -= n;
-    }
-  } else if (z < a.sg.zup) {
-    g = -1;
-    for (int l = 0; l < lv.num_levels; ++l)
-      if (((a.sg.up_mask >> l) & 1) && z < a.sg.up_first[l + 1]) {
-        c = z - a.sg.up_first[l];
-        bytes = (long long)a.N * lv.sn[l] * (long long)sizeof(T);
-        p = reinterpret_cast<char*>(lv.ptr[l]);
-        break;
-      }
-  } else {
-    const int cpi = a.sg.zfirst[a.sg.nseg];
-    const int zz = z - a.sg.zup;
-    const int img = zz / cpi;
-    c = zz - img * cpi;
-    int seg = 0;
-    while (seg + 1 < a.sg.nseg && c >= a.sg.zfirst[seg + 1]) ++seg;
-    c -= a.sg.zfirst[seg];
-    g = img * a.sg.nseg + seg;
-    const int l = a.sg.level[seg];
-    bytes = seg_bytes<T>(lv, a, seg);
-    p = reinterpret_cast<char*>(lv.ptr[l] + (long long)img * lv.sn[l] + (long long)a.sg.row0[seg] * lv.sh[l]);
+  int c = z;
+  for (int l = 0; l < lv.num_levels; ++l) {
+    if ((a.nozero_levels >> l) & 1) continue;
+    bytes = (long long)a.N * lv.sn[l] * (long long)sizeof(T);
+    const int n = (int)((bytes + a.zero_chunk - 1) / a.zero_chunk);
+    if (c < n) { p = reinterpret_cast<char*>(lv.ptr[l]); break; }
+    c -= n;
   }
   if (p) {
     const long long off = (long long)c * a.zero_chunk;
@@ -559,15 +424,7 @@ __device__ __forceinline__ void zero_chunk(const LevelTable<T>& lv, const BwdArg
   }
   __threadfence();
   __syncwarp();
-  if (lane == 0) atomicAdd(g < 0 ? &a.plan->up_done : &a.plan->zero_done[g], 1);
-}
-
-// zero chunks before group g (g may be ngroups: all of them)
-__device__ __forceinline__ int zero_chunks_before(const BwdArgs& a, int g) {
-  if (a.ngroups == 1) return g > 0 ? a.ztotal : 0;
-  if (g >= a.ngroups) return a.ztotal;
-  const int img = g / a.sg.nseg;
-  return a.sg.zup + img * a.sg.zfirst[a.sg.nseg] + a.sg.zfirst[g - img * a.sg.nseg];
+  if (lane == 0) atomicAdd(&a.plan->zero_done, 1);
 }
 
 template <typename T, int CH, int SR, int MODE>
@@ -578,14 +435,13 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 4) roi_align_bwd_sm100_kernel(
   BwdWarpTables& tb = tabs[warp];
   const T* grad = reinterpret_cast<const T*>(a.grad);
   const int tasks_per_roi = a.RP * a.CT;  // MODE 1: RP = kRowChunks
-  const bool sorted = a.ngroups > 1;
   const long long total = a.K * tasks_per_roi;
 
   auto run_task = [&](long long t) {
     const int rp = (int)(t % a.RP);
     const int ct = (int)((t / a.RP) % a.CT);
-    const long long p = t / tasks_per_roi;
-    const long long k = sorted ? (long long)__ldg(a.order + p) : p;
+    const long long k = t / tasks_per_roi;
+    if (a.skip_levels && ((a.skip_levels >> (a.levels ? __ldg(a.levels + k) : 0)) & 1u)) return;
     if (MODE == 1)
       bwd_rows_task<T, CH, SR>(lv, a.rois, a.levels, grad, a.gs_k, a.gs_h, a.gs_w, k, ct, rp, a.N, a.C, a.PH, a.PW,
                                a.aligned, tb, lane);
@@ -600,155 +456,88 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 4) roi_align_bwd_sm100_kernel(
     return;
   }
 
-  // Tasks and zero chunks are both handed out in group order by one global counter each.  Before a
-  // warp scatters a task of group g it (1) helps until every chunk of groups <= g is claimed, (2) waits
-  // until those groups are reported done -- claimed chunks belong to running warps, so this needs no
-  // co-residency -- and after the task it (3) writes one chunk if the fill is less than a group ahead.
+  // Zero chunks and tasks are handed out by one global counter each.  A warp first helps until every chunk
+  // is claimed, waits once until all of them are reported done -- claimed chunks belong to running warps, so
+  // this needs no co-residency -- and then scatters.
   BwdPlan* plan = a.plan;
-  const bool zeroing = a.ztotal > 0;
-  int done_upto = 0;  // groups [0, done_upto) are known to be zero-filled
-  bool all_claimed = false;
-  auto claim_zero = [&]() {
-    int z = 0;
-    if (lane == 0) z = atomicAdd(&plan->zero_ctr, 1);
-    z = __shfl_sync(kFull, z, 0);
-    if (z < a.ztotal) zero_chunk<T>(lv, a, z, lane);
-    return z;
-  };
+  if (a.ztotal > 0) {
+    while (true) {
+      int z = 0;
+      if (lane == 0) z = atomicAdd(&plan->zero_ctr, 1);
+      z = __shfl_sync(kFull, z, 0);
+      if (z >= a.ztotal) break;
+      zero_chunk<T>(lv, a, z, lane);
+    }
+    if (lane == 0)
+      while (ld_acquire(&plan->zero_done) < a.ztotal) __nanosleep(64);
+    __syncwarp();
+    __threadfence();
+  }
   while (true) {
     int t = 0;
     if (lane == 0) t = atomicAdd(&plan->task_ctr, 1);
     t = __shfl_sync(kFull, t, 0);
     if (t >= total) break;
-    const int g = sorted ? __ldg(a.gsorted + t / tasks_per_roi) : 0;
-    if (zeroing) {
-      if (done_upto <= g) {
-        const int need = zero_chunks_before(a, g + 1);
-        while (ld_relaxed(&plan->zero_ctr) < need) claim_zero();
-        all_claimed = need >= a.ztotal;
-        if (lane == 0) {
-          if (done_upto == 0 && sorted)
-            while (ld_acquire(&plan->up_done) < a.sg.zup) __nanosleep(64);
-          for (int q = done_upto; q <= g; ++q) {
-            const int n = zero_chunks_before(a, q + 1) - zero_chunks_before(a, q);
-            while (ld_acquire(&plan->zero_done[q]) < n) __nanosleep(64);
-          }
-        }
-        __syncwarp();
-        __threadfence();
-        done_upto = g + 1;
-      }
-    }
     run_task(t);
-    if (zeroing && !all_claimed) {
-      const int ahead = zero_chunks_before(a, min(g + 1 + a.zlook, a.ngroups));
-      for (int i = 0; i < a.zper; ++i) {
-        const int zc = ld_relaxed(&plan->zero_ctr);
-        all_claimed = zc >= a.ztotal;
-        if (zc >= ahead) break;
-        claim_zero();
-      }
-    }
   }
-  // whatever the RoIs did not reach (groups without RoIs at the end)
-  if (zeroing && !all_claimed)
-    while (ld_relaxed(&plan->zero_ctr) < a.ztotal) claim_zero();
 }
 
 // ---- host side ---------------------------------------------------------------------------------
-// The plan ring is the one allocation this library makes on its own (kPlanSlots x (130 KB + 12 bytes
-// per RoI) per device, first backward call, regrown when a call brings more RoIs).  If it cannot be
-// had (e.g. the first call happens inside a stream capture) the call falls back to memset + static
-// task assignment.
+// The plan ring is the one allocation the scatter path makes on its own (kPlanSlots x 384 bytes per
+// device, first backward call).  Slots are handed out under a mutex; every slot carries the event of its
+// last user and the next user's stream waits for it, so calls on different streams or from different host
+// threads never share a live plan.  If the ring cannot be had (e.g. the first call happens inside a
+// stream capture) the call falls back to memset + static task assignment.
+struct PlanSlot {
+  cudaEvent_t done = nullptr;
+  bool used = false;
+};
 struct DeviceScratch {
   char* buf = nullptr;
-  size_t slot_bytes = 0;
-  long long kcap = 0;
+  PlanSlot slot[kPlanSlots];
   unsigned next = 0;
-  int l2_bytes = 0;
   int sms = 0;
   bool tried = false;
 };
 DeviceScratch g_scratch[64];
-std::vector<void*>* g_outgrown = nullptr;  // freed at release: kernels in flight may still use them
+std::mutex g_scratch_mutex;
 
-constexpr size_t kPlanHead = (sizeof(BwdPlan) + 255) & ~(size_t)255;
+constexpr size_t kPlanBytes = (sizeof(BwdPlan) + 255) & ~(size_t)255;
 
-DeviceScratch* scratch_for_current_device() {
+// plan slot for this call (its stream already waits for the slot's previous user); nullptr when it cannot be had
+BwdPlan* plan_slot(cudaStream_t st, int* sms, PlanSlot** out) {
   int dev = 0;
+  *sms = 148;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(g_scratch_mutex);
   DeviceScratch& s = g_scratch[dev];
   if (!s.tried) {
     s.tried = true;
-    cudaDeviceGetAttribute(&s.l2_bytes, cudaDevAttrL2CacheSize, dev);
     cudaDeviceGetAttribute(&s.sms, cudaDevAttrMultiProcessorCount, dev);
-  }
-  return &s;
-}
-
-// plan slot for a call with K RoIs: head, then gid[K], order[K]; nullptr when memory cannot be had
-BwdPlan* plan_slot(DeviceScratch* s, long long K) {
-  if (!s) return nullptr;
-  if (!s->buf || K > s->kcap) {
-    const long long kcap = K + K / 2 + 4096;
-    const size_t slot = kPlanHead + (((size_t)kcap * 12 + 255) & ~(size_t)255);
     void* p = nullptr;
-    if (cudaMalloc(&p, slot * kPlanSlots) != cudaSuccess) {
-      (void)cudaGetLastError();
-      return nullptr;
-    }
-    if (s->buf) {
-      if (!g_outgrown) g_outgrown = new std::vector<void*>();
-      g_outgrown->push_back(s->buf);
-    }
-    s->buf = (char*)p;
-    s->slot_bytes = slot;
-    s->kcap = kcap;
+    if (cudaMalloc(&p, kPlanBytes * kPlanSlots) != cudaSuccess) (void)cudaGetLastError();
+    else s.buf = (char*)p;
   }
-  return (BwdPlan*)(s->buf + s->slot_bytes * (s->next++ % kPlanSlots));
+  if (s.sms > 0) *sms = s.sms;
+  if (!s.buf) return nullptr;
+  const unsigned i = s.next++ % kPlanSlots;
+  PlanSlot& sl = s.slot[i];
+  if (!sl.done && cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming) != cudaSuccess) {
+    (void)cudaGetLastError();
+    sl.done = nullptr;
+    return nullptr;
+  }
+  if (sl.used && cudaStreamWaitEvent(st, sl.done, 0) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return nullptr;
+  }
+  *out = &sl;
+  return (BwdPlan*)(s.buf + kPlanBytes * i);
 }
 
 int env_int(const char* name, int dflt) {
   const char* s = getenv(name);
   return s ? atoi(s) : dflt;
-}
-
-// Cuts every level whose map (one image) is at most `up_bytes` into bands of at most `budget` bytes; bigger
-// levels are filled up front and their RoIs ride with the image's last segment.  False when nothing is
-// left to segment or it needs too many segments.
-bool make_segments(const LevelArgs& lv, size_t es, double budget, double up_bytes, SegTable* sg) {
-  sg->nseg = 0;
-  sg->up_mask = 0;
-  for (int li = 0; li < lv.num_levels; ++li) {
-    const int l = lv.num_levels - 1 - li;  // coarse levels first
-    const long long H = lv.height[l];
-    const double row_bytes = (double)lv.width[l] * (double)lv.channels * (double)es;
-    if (row_bytes * (double)H > up_bytes) {
-      sg->up_mask |= 1 << l;
-      continue;
-    }
-    long long band = (long long)(budget / row_bytes);
-    if (band < 1) band = 1;
-    long long nb = (H + band - 1) / band;
-    band = (H + nb - 1) / nb;  // equal bands
-    nb = (H + band - 1) / band;
-    if (sg->nseg + nb > kMaxSegs) return false;
-    sg->first_seg[l] = sg->nseg;
-    sg->band_rows[l] = (int)band;
-    sg->nbands[l] = (int)nb;
-    for (long long b = 0; b < nb; ++b) {
-      const int i = sg->nseg++;
-      sg->level[i] = l;
-      sg->row0[i] = (int)(b * band);
-      sg->rows[i] = (int)((b + 1) * band <= H ? band : H - b * band);
-    }
-  }
-  if (sg->nseg == 0) return false;
-  for (int l = 0; l < B200DET_MAX_LEVELS; ++l)
-    if (l >= lv.num_levels || ((sg->up_mask >> l) & 1)) {
-      sg->first_seg[l] = sg->nseg - 1; sg->band_rows[l] = 0x7fffffff; sg->nbands[l] = 1;
-    }
-  return true;
 }
 
 template <typename T, int CH, int SR, int MODE>
@@ -773,11 +562,11 @@ int launch_bwd_k(const LevelTable<T>& tab, const BwdArgs& a, int sms, cudaStream
 }
 
 template <typename T>
-int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool vec, const void* rois,
-               const int32_t* levels, long long K, int C, int PH, int PW, int sr, bool aligned, bool zero_init,
-               cudaStream_t st) {
+int launch_bwd_one(const LevelArgs& lv, const void* grad, const int64_t* gs, bool vec, const void* rois,
+                   const int32_t* levels, long long K, int C, int PH, int PW, int sr, bool aligned, bool zero_init,
+                   unsigned skip_levels, unsigned nozero_levels, int mode, cudaStream_t st) {
   const LevelTable<T> tab = make_nhwc_table<T>(lv);
-  const int CH = (C % 256 == 0 && env_int("B200DET_BWD_CH", 8) == 8) ? 8 : 4;
+  const int CH = C % 256 == 0 ? 8 : 4;
   BwdArgs a;
   a.rois = (const float*)rois;
   a.levels = levels;
@@ -786,97 +575,35 @@ int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool ve
   a.K = K;
   a.N = (int)lv.batch; a.C = C; a.PH = PH; a.PW = PW;
   a.CT = C / (32 * CH);
-  // Row gather (one red per footprint pixel) needs vector gradient loads and a lane per y sample.
-  // Measured on B200 (profiles/r01_bwd_rows_segments.md): it wins for box-head shapes (7x7 bins, samples
-  // >= 1 pixel apart: a pooled-row pair spreads over up to 8 feature rows) and loses for the mask-head
-  // shape (14x14: the upstream gradient is re-read 2.5x and half of those re-reads miss L2), so by
-  // default it is taken when a RoI has at most 16 y samples.  B200DET_BWD_MODE=0 / 1 forces one.
-  const int mode_env = env_int("B200DET_BWD_MODE", -1);
-  const bool rows_ok = vec && PH * sr <= 32;
-  a.mode = rows_ok && (mode_env == 1 || (mode_env < 0 && PH * sr <= 16)) ? 1 : 0;
+  a.skip_levels = skip_levels;
+  a.nozero_levels = nozero_levels;
+  a.mode = mode;
   a.RP = a.mode == 1 ? kRowChunks : (PH + 1) / 2;
   a.vec = vec; a.aligned = aligned;
-  a.plan = nullptr; a.order = nullptr; a.gsorted = nullptr; a.ngroups = 1; a.zero_chunk = 0; a.ztotal = 0; a.zlook = 1; a.zper = 1;
-  a.sg.nseg = 0; a.sg.zup = 0; a.sg.up_mask = 0;
+  a.plan = nullptr; a.zero_chunk = 0; a.ztotal = 0;
 
-  DeviceScratch* s = scratch_for_current_device();
-  const int sms = s && s->sms > 0 ? s->sms : 148;
+  int sms = 148;
+  PlanSlot* slot = nullptr;
   const long long total = K * a.RP * a.CT;
-  size_t image_bytes = 0;
-  for (int l = 0; l < lv.num_levels; ++l) image_bytes += (size_t)lv.height[l] * lv.width[l] * C * sizeof(T);
-  const bool dynamic = total < 0x7fffffffLL && K < 0x7fffffffLL && lv.batch <= 0x7fffffffLL &&
-                       env_int("B200DET_BWD_FUSED", 1) != 0;
-  BwdPlan* plan = dynamic ? plan_slot(s, K) : nullptr;
+  BwdPlan* plan = total < 0x7fffffffLL ? plan_slot(st, &sms, &slot) : nullptr;
+  size_t fill_bytes = 0;
+  for (int l = 0; l < lv.num_levels; ++l)
+    if (!((nozero_levels >> l) & 1)) fill_bytes += (size_t)lv.batch * lv.height[l] * lv.width[l] * C * sizeof(T);
   if (plan) {
-    // Segmented mode (default; B200DET_BWD_PHASED=0 turns it off): RoIs are counting-sorted by
-    // (image, level, band of rows) and the persistent grid works group by group, zero-filling group
-    // g+1 while it scatters group g, so the reds land on lines that are still dirty in L2 and every
-    // gradient line goes to HBM once.  A band is B200DET_BWD_GROUP_MB megabytes (default 20: the 126 MB
-    // L2 behaves like ~60 MB for data every SM touches, profiles/r01_bwd_phased.md, and two groups plus the
-    // streaming upstream gradient share it).
-    const double budget = (double)env_int("B200DET_BWD_GROUP_MB", 20) * 1048576.0;
-    bool seg = env_int("B200DET_BWD_PHASED", 0) != 0 && (double)image_bytes * (double)a.N > budget &&
-               make_segments(lv, sizeof(T), budget, (double)env_int("B200DET_BWD_UP_MB", 32) * 1048576.0, &a.sg);
-    if (seg && (long long)a.sg.nseg * a.N > kMaxGroups) seg = false;
-    if (!seg) a.sg.nseg = 0;
-    a.ngroups = seg ? a.sg.nseg * a.N : 1;
     B200DET_CUDA_OK(cudaMemsetAsync(plan, 0, sizeof(BwdPlan), st));
-    if (seg) {
-      int* gid = reinterpret_cast<int*>(reinterpret_cast<char*>(plan) + kPlanHead);
-      int* order = gid + s->kcap;
-      int* gsorted = order + s->kcap;
-      const LevelTable<float> ftab = make_nhwc_table<float>(lv);
-      const int th = 128, bl = (int)((K + th - 1) / th);
-      if (sr == 1)
-        bwd_plan_gid_kernel<1><<<bl, th, 0, st>>>(ftab, a.sg, (const float*)rois, levels, (int)K, a.N, PH, PW, aligned,
-                                                  gid, plan);
-      else
-        bwd_plan_gid_kernel<2><<<bl, th, 0, st>>>(ftab, a.sg, (const float*)rois, levels, (int)K, a.N, PH, PW, aligned,
-                                                  gid, plan);
-      bwd_plan_scan_kernel<<<1, 1024, 0, st>>>(plan, a.ngroups);
-      bwd_plan_fill_kernel<<<bl, th, 0, st>>>(gid, (int)K, plan, order, gsorted);
-      B200DET_CUDA_OK(cudaGetLastError());
-      a.order = order;
-      a.gsorted = gsorted;
-    }
     a.plan = plan;
-    if (zero_init) {
-      // one zero chunk per ~0.75 tasks so the fill hides behind the scatter of the previous group
-      a.zlook = env_int("B200DET_BWD_ZLOOK", 2);
-      a.zper = env_int("B200DET_BWD_ZPER", 3);
-      // segmented: one zero chunk per ~0.75 tasks so the fill keeps pace with the scatter; one group: the
-      // fill is a phase of its own in front, and big chunks are faster (measured: 16 KB 1.07 ms, 27 KB 1.00,
-      // 51 KB 0.96 for cfg3 fp32), so about four chunks per resident warp
-      double zc = seg ? (double)image_bytes * (double)a.N /
-                            (0.01 * env_int("B200DET_BWD_ZTASKS_PCT", 75) * (double)(total > 1 ? total : 1))
-                      : (double)image_bytes * (double)a.N / ((double)sms * 16.0 * env_int("B200DET_BWD_ZPER_WARP", 4));
-      long long zero_chunk = ((long long)zc + 4095) / 4096 * 4096;
+    if (zero_init && fill_bytes) {
+      // the fill is a phase of its own in front, and big chunks are faster (measured: 16 KB 1.07 ms, 27 KB
+      // 1.00, 51 KB 0.96 for cfg3 fp32), so about four chunks per resident warp
+      long long zero_chunk = ((long long)((double)fill_bytes / ((double)sms * 64.0)) + 4095) / 4096 * 4096;
       if (zero_chunk < 16384) zero_chunk = 16384;
       if (zero_chunk > (1 << 20)) zero_chunk = 1 << 20;
       a.zero_chunk = (int)zero_chunk;
       long long zt = 0;
-      if (seg) {
-        a.sg.up_first[0] = 0;
-        for (int l = 0; l < B200DET_MAX_LEVELS; ++l) {
-          long long n = 0;
-          if (l < lv.num_levels && ((a.sg.up_mask >> l) & 1))
-            n = ((long long)a.N * lv.height[l] * lv.width[l] * C * (long long)sizeof(T) + zero_chunk - 1) / zero_chunk;
-          if (a.sg.up_first[l] + n >= 0x7fffffffLL) return 1;
-          a.sg.up_first[l + 1] = a.sg.up_first[l] + (int)n;
-        }
-        a.sg.zup = a.sg.up_first[B200DET_MAX_LEVELS];
-        for (int i = 0; i < a.sg.nseg; ++i) {
-          const long long bytes = (long long)a.sg.rows[i] * lv.width[a.sg.level[i]] * C * (long long)sizeof(T);
-          a.sg.zfirst[i] = (int)zt;
-          zt += (bytes + zero_chunk - 1) / zero_chunk;
-        }
-        a.sg.zfirst[a.sg.nseg] = (int)zt;
-        zt = zt * a.N + a.sg.zup;
-      } else {
-        for (int l = 0; l < lv.num_levels; ++l) {
-          const long long bytes = (long long)a.N * lv.height[l] * lv.width[l] * C * (long long)sizeof(T);
-          zt += (bytes + zero_chunk - 1) / zero_chunk;
-        }
+      for (int l = 0; l < lv.num_levels; ++l) {
+        if ((nozero_levels >> l) & 1) continue;
+        const long long bytes = (long long)a.N * lv.height[l] * lv.width[l] * C * (long long)sizeof(T);
+        zt += (bytes + zero_chunk - 1) / zero_chunk;
       }
       if (zt >= 0x7fffffffLL) return 1;  // cannot happen: >= 16 KB per chunk
       a.ztotal = (int)zt;
@@ -884,19 +611,46 @@ int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool ve
   } else if (zero_init) {
     for (int l = 0; l < lv.num_levels; ++l) {
       const size_t bytes = (size_t)lv.batch * lv.channels * lv.height[l] * lv.width[l] * sizeof(T);
-      if (bytes) B200DET_CUDA_OK(cudaMemsetAsync(lv.ptr[l], 0, bytes, st));
+      if (bytes && !((nozero_levels >> l) & 1)) B200DET_CUDA_OK(cudaMemsetAsync(lv.ptr[l], 0, bytes, st));
     }
   }
+  int rc;
   if (CH == 8)
-    return sr == 1 ? launch_bwd_k<T, 8, 1>(tab, a, sms, st) : launch_bwd_k<T, 8, 2>(tab, a, sms, st);
-  return sr == 1 ? launch_bwd_k<T, 4, 1>(tab, a, sms, st) : launch_bwd_k<T, 4, 2>(tab, a, sms, st);
+    rc = sr == 1 ? launch_bwd_k<T, 8, 1>(tab, a, sms, st) : launch_bwd_k<T, 8, 2>(tab, a, sms, st);
+  else
+    rc = sr == 1 ? launch_bwd_k<T, 4, 1>(tab, a, sms, st) : launch_bwd_k<T, 4, 2>(tab, a, sms, st);
+  if (slot) {
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (cudaEventRecord(slot->done, st) == cudaSuccess) slot->used = true;
+    else (void)cudaGetLastError();
+  }
+  return rc;
+}
+
+// Two task shapes (file header): the pooled-row PAIR sweep (MODE 0) and the feature-ROW gather (MODE 1, one red
+// per footprint pixel but the upstream gradient re-read by every feature row a pooled row taps).  Measured on
+// B200 (profiles/r01_bwd_rows_segments.md): the row gather wins for box-head shapes (7x7 bins, samples >= 1 pixel
+// apart: a pooled-row pair spreads over up to 8 feature rows) and loses for the mask-head shape (14x14: the
+// re-reads evict the gradient lines the reds work on), so it is taken when a RoI has at most 16 y samples.
+// Choosing the shape per pyramid level (row gather for the dense coarse levels only, two launches) was measured
+// in round 2 and lost as well (0.97 -> 1.12-1.19 ms on cfg3, profiles/r02_bwd_study.md).  B200DET_BWD_MODE=0 / 1
+// forces one shape (tests/test_roi_align_gpu.py runs both on every fast-path case).
+template <typename T>
+int launch_bwd(const LevelArgs& lv, const void* grad, const int64_t* gs, bool vec, const void* rois,
+               const int32_t* levels, long long K, int C, int PH, int PW, int sr, bool aligned, bool zero_init,
+               unsigned skip_levels, cudaStream_t st) {
+  const int mode_env = env_int("B200DET_BWD_MODE", -1);
+  const bool rows_ok = vec && PH * sr <= 32;
+  const int mode = rows_ok && (mode_env == 1 || (mode_env < 0 && PH * sr <= 16)) ? 1 : 0;
+  return launch_bwd_one<T>(lv, grad, gs, vec, rois, levels, K, C, PH, PW, sr, aligned, zero_init, skip_levels,
+                           skip_levels, mode, st);
 }
 
 }  // namespace
 
 int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs, const void* rois,
                        const int32_t* levels, long long K, int PH, int PW, int sr, bool aligned, bool zero_init,
-                       cudaStream_t st, int* taken) {
+                       unsigned skip_levels, cudaStream_t st, int* taken) {
   *taken = 0;
   if (!sm100_eligible(lv, dtype, PH, PW, sr)) return 0;
   if (K == 0 || lv.batch == 0) return 0;  // nothing to scatter: the caller's memset path handles it
@@ -908,9 +662,9 @@ int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const i
   const int C = (int)lv.channels;
   int rc = 0;
   switch (dtype) {
-    case B200DET_F32: rc = launch_bwd<float>(lv, grad, gs, vec, rois, levels, K, C, PH, PW, sr, aligned, zero_init, st); break;
-    case B200DET_F16: rc = launch_bwd<__half>(lv, grad, gs, vec, rois, levels, K, C, PH, PW, sr, aligned, zero_init, st); break;
-    case B200DET_BF16: rc = launch_bwd<__nv_bfloat16>(lv, grad, gs, vec, rois, levels, K, C, PH, PW, sr, aligned, zero_init, st); break;
+    case B200DET_F32: rc = launch_bwd<float>(lv, grad, gs, vec, rois, levels, K, C, PH, PW, sr, aligned, zero_init, skip_levels, st); break;
+    case B200DET_F16: rc = launch_bwd<__half>(lv, grad, gs, vec, rois, levels, K, C, PH, PW, sr, aligned, zero_init, skip_levels, st); break;
+    case B200DET_BF16: rc = launch_bwd<__nv_bfloat16>(lv, grad, gs, vec, rois, levels, K, C, PH, PW, sr, aligned, zero_init, skip_levels, st); break;
     default: return 0;
   }
   if (rc) return rc;
@@ -919,19 +673,19 @@ int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const i
 }
 
 void roi_align_bwd_release() {
+  std::lock_guard<std::mutex> lock(g_scratch_mutex);
   int cur = 0;
   cudaGetDevice(&cur);
-  for (int d = 0; d < 64; ++d)
-    if (g_scratch[d].buf) {
-      cudaSetDevice(d);
-      cudaFree(g_scratch[d].buf);
-      g_scratch[d] = DeviceScratch();
-    }
-  cudaSetDevice(cur);
-  if (g_outgrown) {
-    for (void* p : *g_outgrown) cudaFree(p);
-    g_outgrown->clear();
+  for (int d = 0; d < 64; ++d) {
+    DeviceScratch& s = g_scratch[d];
+    if (!s.buf && !s.tried) continue;
+    cudaSetDevice(d);
+    if (s.buf) cudaFree(s.buf);
+    for (int i = 0; i < kPlanSlots; ++i)
+      if (s.slot[i].done) cudaEventDestroy(s.slot[i].done);
+    s = DeviceScratch();
   }
+  cudaSetDevice(cur);
 }
 
 }  // namespace b200det

@@ -67,6 +67,7 @@ struct TileGeom {
   int base[B200DET_MAX_LEVELS + 1];
   int tiles_y[B200DET_MAX_LEVELS], tiles_x[B200DET_MAX_LEVELS];
   int tw;
+  unsigned level_mask;   // bit l: this launch produces level l (the others belong to the scatter kernel)
 };
 
 struct StripArgs {
@@ -126,7 +127,7 @@ __global__ void strip_plan_kernel(LevelTable<float> lv, const float* __restrict_
   rc.level = l;
   rc.batch = b;
   recs[k] = rc;
-  if (in_range && yb >= ya && xb >= xa) {  // one more RoI in the list of every tile the footprint overlaps
+  if (in_range && yb >= ya && xb >= xa && ((tg.level_mask >> l) & 1u)) {  // one more RoI in the list of every tile its footprint overlaps
     const int t0 = tg.base[l] + b * tg.tiles_y[l] * tg.tiles_x[l];
     for (int ty = ya / kTileRows; ty <= yb / kTileRows; ++ty)
       for (int tx = xa / tg.tw; tx <= xb / tg.tw; ++tx) atomicAdd(tile_cnt + t0 + ty * tg.tiles_x[l] + tx, 1);
@@ -647,8 +648,8 @@ int launch_strip_k(const LevelTable<T>& tab, const StripArgs& a, int sms, cudaSt
 
 template <typename T>
 int launch_strip(const LevelArgs& lv, const void* grad, const int64_t* gs, const void* rois, const int32_t* levels,
-                 long long K, int C, int PH, int PW, int sr, bool aligned, bool zero_init, cudaStream_t st,
-                 int* taken) {
+                 long long K, int C, int PH, int PW, int sr, bool aligned, bool zero_init, unsigned level_mask,
+                 cudaStream_t st, int* taken) {
   const int CH = (C % 256 == 0 && senv_int("B200DET_STRIP_CH", 8) == 8) ? 8 : 4;
   const int TW = CH == 8 ? StripShape<8>::TW : StripShape<4>::TW;
   StripArgs a;
@@ -663,7 +664,7 @@ int launch_strip(const LevelArgs& lv, const void* grad, const int64_t* gs, const
     const int l = lv.num_levels - 1 - li;
     a.strips_x[l] = (int)((lv.width[l] + TW - 1) / TW);
     a.job_base[li] = (int)jobs;
-    jobs += (long long)a.strips_x[l] * lv.height[l] * lv.batch * a.CT;
+    if ((level_mask >> l) & 1u) jobs += (long long)a.strips_x[l] * lv.height[l] * lv.batch * a.CT;
     if (jobs > 0x7fffffffLL) return 0;
   }
   for (int li = lv.num_levels; li <= B200DET_MAX_LEVELS; ++li) a.job_base[li] = (int)jobs;
@@ -671,6 +672,7 @@ int launch_strip(const LevelArgs& lv, const void* grad, const int64_t* gs, const
   // tiles (kTileRows x TW) and their RoI lists
   long long tiles = 0;
   a.tg.tw = TW;
+  a.tg.level_mask = level_mask;
   for (int l = 0; l < B200DET_MAX_LEVELS; ++l) {
     a.tg.base[l] = (int)tiles;
     a.tg.tiles_y[l] = a.tg.tiles_x[l] = 1;
@@ -726,9 +728,11 @@ int launch_strip(const LevelArgs& lv, const void* grad, const int64_t* gs, const
 
 int roi_align_bwd_strip(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs, const void* rois,
                         const int32_t* levels, long long K, int PH, int PW, int sr, bool aligned, bool zero_init,
-                        cudaStream_t st, int* taken) {
+                        unsigned level_mask, cudaStream_t st, int* taken) {
   *taken = 0;
   if (!sm100_eligible(lv, dtype, PH, PW, sr)) return 0;
+  level_mask &= (1u << lv.num_levels) - 1u;
+  if (!level_mask) return 0;
   if (K == 0 || lv.batch == 0 || K > 0x7fffffffLL / 64 || lv.batch > kMaxImagesS) return 0;
   const size_t es = dtype_size(dtype);
   const long long per16 = 16 / (long long)es;
@@ -741,9 +745,9 @@ int roi_align_bwd_strip(const LevelArgs& lv, int dtype, const void* grad, const 
     if (lv.height[l] > 0x7ffe || lv.width[l] > 0x7ffe) return 0;
   const int C = (int)lv.channels;
   switch (dtype) {
-    case B200DET_F32: return launch_strip<float>(lv, grad, gs, rois, levels, K, C, PH, PW, sr, aligned, zero_init, st, taken);
-    case B200DET_F16: return launch_strip<__half>(lv, grad, gs, rois, levels, K, C, PH, PW, sr, aligned, zero_init, st, taken);
-    case B200DET_BF16: return launch_strip<__nv_bfloat16>(lv, grad, gs, rois, levels, K, C, PH, PW, sr, aligned, zero_init, st, taken);
+    case B200DET_F32: return launch_strip<float>(lv, grad, gs, rois, levels, K, C, PH, PW, sr, aligned, zero_init, level_mask, st, taken);
+    case B200DET_F16: return launch_strip<__half>(lv, grad, gs, rois, levels, K, C, PH, PW, sr, aligned, zero_init, level_mask, st, taken);
+    case B200DET_BF16: return launch_strip<__nv_bfloat16>(lv, grad, gs, rois, levels, K, C, PH, PW, sr, aligned, zero_init, level_mask, st, taken);
   }
   return 0;
 }
