@@ -99,10 +99,15 @@ static int backward_impl(const LevelArgs& lv, int dtype, const void* grad, const
     // Which kernel produces which level.  The write-once strip kernel (shared-memory accumulators, every
     // gradient byte stored once, deterministic) takes the levels whose maps are too big for L2 to act as the
     // accumulator: there a red costs a zero fill, a DRAM read-modify-write and a write-back per line.  The
-    // vector-red scatter takes the rest (dense, L2-resident coarse levels).  B200DET_BWD_STRIP=1 / 0 forces
-    // everything / nothing onto the strips; the deterministic flag means strips for every level.
-    static const int strip_env = getenv("B200DET_BWD_STRIP") ? atoi(getenv("B200DET_BWD_STRIP")) : -1;
-    static const double strip_min_mb = getenv("B200DET_STRIP_MIN_MB") ? atof(getenv("B200DET_STRIP_MIN_MB")) : 1e30;
+    // vector-red scatter takes the rest (dense, L2-resident coarse levels).  Measured on B200
+    // (profiles/r02_bwd_study.md) the strips do not beat the scatter on any BASELINE shape yet, so by default no
+    // level is big enough (B200DET_STRIP_MIN_MB=<MB of one level, whole batch> lowers the bar); B200DET_BWD_STRIP=1
+    // / 0 forces everything / nothing onto the strips; the deterministic flag means strips for every level.
+    // (read per call, like B200DET_BWD_MODE: the parity tests switch them inside one process)
+    const char* se = getenv("B200DET_BWD_STRIP");
+    const char* sm = getenv("B200DET_STRIP_MIN_MB");
+    const int strip_env = se ? atoi(se) : -1;
+    const double strip_min_mb = sm ? atof(sm) : 1e30;
     const unsigned all_levels = (1u << lv.num_levels) - 1u;
     unsigned strip_levels = 0;
     if (deterministic || strip_env == 1) {

@@ -74,13 +74,10 @@ bool image_starts(const void* rois, int dtype, int64_t K, int64_t N, std::vector
 // how many image chunks the host entry points pipeline over (H2D of chunk c+1, kernels of chunk c and
 // D2H of chunk c-1 overlap; PCIe is full duplex).  B200DET_HOST_CHUNKS overrides (1 = no pipelining).
 int host_chunks(int64_t N) {
-  static int env = -1;
-  if (env < 0) {
-    const char* e = getenv("B200DET_HOST_CHUNKS");
-    env = e ? atoi(e) : 16;
-    if (env < 1) env = 1;
-    if (env > kMaxChunks) env = kMaxChunks;
-  }
+  const char* e = getenv("B200DET_HOST_CHUNKS");  // read per call: the tests run 1, 3 and the default in one process
+  int env = e ? atoi(e) : 16;
+  if (env < 1) env = 1;
+  if (env > kMaxChunks) env = kMaxChunks;
   return (int)(N < env ? (N > 0 ? N : 1) : env);
 }
 

@@ -34,19 +34,11 @@
 namespace b200det {
 namespace {
 
-// warps per CTA (>= 2: warps 0 and 1 build the tables).  B200DET_FWD_WARPS overrides (2..4).
+// warps per CTA (>= 2: warps 0 and 1 build the tables); 2..4 were measured (profiles/r01_kbench_fwd_v3_warps_sweep.log), 4 wins.
 // Register budget: 128 per thread for fp32 (16 warps/SM); 96 for 16-bit I/O (20 warps/SM) -- measured
 // on B200: fp32 loses 15% at 96 registers (spills), bf16 gains 6%.
-int fwd_warps() {
-  static int nw = 0;
-  if (!nw) {
-    const char* s = getenv("B200DET_FWD_WARPS");
-    nw = s ? atoi(s) : 4;
-    if (nw < 2) nw = 2;
-    if (nw > 4) nw = 4;  // the kernel is compiled for at most 128 threads
-  }
-  return nw;
-}
+constexpr int kFwdWarps = 4;
+int fwd_warps() { return kFwdWarps; }
 struct __align__(16) FwdTables {
   XTab x;
   int y_nr[kMaxPH];                     // distinct feature rows of pooled row ph

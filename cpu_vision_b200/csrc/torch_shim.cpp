@@ -76,10 +76,8 @@ bool fast_shape(int dt, int64_t C, int64_t PH, int64_t PW, int64_t sr) {
          PH >= 1 && PH <= 32;
 }
 bool relayout_pays(int64_t K, int64_t PH, int64_t PW, int64_t feature_pixels) {
-  static const bool on = [] {
-    const char* e = getenv("B200DET_NCHW_RELAYOUT");
-    return !e || atoi(e) != 0;
-  }();
+  const char* e = getenv("B200DET_NCHW_RELAYOUT");  // read per call (the tests compare both paths in one process)
+  const bool on = !e || atoi(e) != 0;
   // a generic output element costs about as much as 16 feature elements of re-layout
   return on && K > 0 && K * PH * PW * 16 >= feature_pixels;
 }

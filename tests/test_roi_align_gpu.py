@@ -386,8 +386,8 @@ def _bwd_case(seed, N=3, C=256, H=40, W=56, K=200, PH=7, scale=0.25, lo=8.0, sor
 
 
 @pytest.mark.parametrize("ph,scale,lo", [(7, 0.25, 8.0), (14, 0.25, 16.0), (7, 0.0625, 4.0)])
-def test_backward_deterministic_tile_kernel(capi, ph, scale, lo):
-    """B200DET_BWD_DETERMINISTIC: tile accumulation, no atomics -- bitwise reproducible and equal to the
+def test_backward_deterministic_kernel(capi, ph, scale, lo):
+    """B200DET_BWD_DETERMINISTIC: strip accumulation in shared memory, no atomics -- bitwise reproducible and equal to the
     fp64 oracle within fp32 rounding (the role of ops/roi_align.py:251-255 in the reference)."""
     rois, go, want64, (N, C, H, W, PH, sc) = _bwd_case(11 + ph, PH=ph, scale=scale, lo=lo)
     god = go.to(DEV).contiguous(memory_format=torch.channels_last)
@@ -453,10 +453,17 @@ def test_deterministic_mode_through_the_dispatcher():
         torch.use_deterministic_algorithms(False)
 
 
+@pytest.mark.parametrize("chunks", [None, "1", "3"])
 @pytest.mark.parametrize("channels_last", [False, True])
-def test_msroi_align_host_entry_points_pipelined(golden, capi, channels_last):
+def test_msroi_align_host_entry_points_pipelined(golden, capi, channels_last, chunks, monkeypatch):
     """b200det_msroi_align_{forward,backward}_host: CPU tensors in/out, pipelined over image chunks
-    (H2D / kernels / D2H overlap); results must equal the reference fixtures and the device entry points."""
+    (H2D / kernels / D2H overlap); results must equal the reference fixtures and the device entry points.
+    B200DET_HOST_CHUNKS (read per call) sets the number of chunks: default (one per image here), 1 (no
+    pipelining) and 3 (uneven chunks) must all give the same answer."""
+    if chunks is None:
+        monkeypatch.delenv("B200DET_HOST_CHUNKS", raising=False)
+    else:
+        monkeypatch.setenv("B200DET_HOST_CHUNKS", chunks)
     d = golden("msroi_align.pt")
     boxes = d["boxes"]
     rois = torch.cat([torch.cat([torch.full((len(b), 1), float(i)), b], 1) for i, b in enumerate(boxes)])
@@ -520,6 +527,27 @@ def test_nchw_caller_takes_the_fast_kernels_through_the_dispatcher():
     few = rois[:2].to(DEV)
     close_fwd(torch.ops.torchvision.roi_align(x.to(DEV), few, 0.0625, PH, PH, 2, True),
               oracle.roi_align_forward(x, rois[:2], PH, PH, 0.0625, 2, True))
+
+
+def test_nchw_relayout_switch(monkeypatch):
+    """B200DET_NCHW_RELAYOUT=0 keeps an NCHW caller on the generic strided kernels: same values (forward within
+    the forward bar, backward within the reordering bar) as the re-layout path."""
+    import cpu_vision_b200  # noqa: F401
+
+    g = torch.Generator().manual_seed(22)
+    N, C, H, W, K, PH = 2, 128, 40, 56, 200, 7
+    x = torch.randn(N, C, H, W, generator=g).to(DEV)
+    rois = rand_rois(g, K, N, W * 8.0, H * 8.0, lo=8.0).to(DEV)
+    go = torch.randn(K, C, PH, PH, generator=g).to(DEV)
+    res = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("B200DET_NCHW_RELAYOUT", flag)
+        xd = x.clone().requires_grad_(True)
+        y = torch.ops.torchvision.roi_align(xd, rois, 0.125, PH, PH, 2, False)
+        y.backward(go)
+        res[flag] = (y.detach(), xd.grad)
+    close_fwd(res["0"][0], res["1"][0].cpu())
+    close_bwd(res["0"][1], res["1"][1].cpu().double())
 
 
 def test_nchw_msroi_module_through_relayout(golden):
