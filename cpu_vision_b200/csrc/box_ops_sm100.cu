@@ -24,8 +24,10 @@ __global__ void clip_filter_kernel(const T* __restrict__ boxes, const T* __restr
     if ((long long)__ldg(off + mid) <= i) lo = mid; else hi = mid;
   }
   const float h = __ldg(sizes + 2 * lo), w = __ldg(sizes + 2 * lo + 1);
-  // clamp(min=0, max=size) in the boxes' dtype, like Tensor.clamp
-  auto clampT = [](float v, float m) { return fminf(fmaxf(v, 0.f), m); };
+  // clamp(min=0, max=size) in the boxes' dtype, like Tensor.clamp: a NaN coordinate stays NaN (fminf / fmaxf would
+  // turn it into 0), so ws / hs are NaN, `>= min_size` is false and the box is removed like in the reference
+  // (boxes.py:137-139,167-168)
+  auto clampT = [](float v, float m) { return v != v ? v : fminf(fmaxf(v, 0.f), m); };
   const T x1 = Io<T>::to(clampT((float)Io<T>::ld(boxes + i * 4 + 0), w)), y1 = Io<T>::to(clampT((float)Io<T>::ld(boxes + i * 4 + 1), h));
   const T x2 = Io<T>::to(clampT((float)Io<T>::ld(boxes + i * 4 + 2), w)), y2 = Io<T>::to(clampT((float)Io<T>::ld(boxes + i * 4 + 3), h));
   out[i * 4 + 0] = x1; out[i * 4 + 1] = y1; out[i * 4 + 2] = x2; out[i * 4 + 3] = y2;

@@ -219,6 +219,9 @@ int b200det_msroi_align_forward(const void* const* feats, const int64_t* heights
       if (rc) return rc;
     }
     lv_ids = levels;
+  } else if (levels && !levels_given && K > 0) {
+    // one level: every RoI maps to level 0 (callers keep the buffer for the backward)
+    B200DET_CUDA_OK(cudaMemsetAsync(levels, 0, (size_t)K * sizeof(int32_t), (cudaStream_t)stream));
   }
   return forward_impl(lv, dtype, rois, lv_ids, output, out_layout, K, PH, PW, sampling_ratio,
                       aligned, (cudaStream_t)stream);

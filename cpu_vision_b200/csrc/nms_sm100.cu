@@ -976,11 +976,24 @@ __global__ void nms_seg_keys_kernel(const T* __restrict__ scores, const uint8_t*
 template <typename T>
 __global__ void nms_seg_max_kernel(const T* __restrict__ boxes, const int64_t* __restrict__ idxs,
                                    const uint8_t* __restrict__ valid, const int32_t* __restrict__ off,
-                                   const int32_t* __restrict__ smode, float* __restrict__ out,
+                                   int32_t* __restrict__ smode, float* __restrict__ out,
                                    int32_t* __restrict__ sgroup, int thr_nonneg) {
   __shared__ float red[32];
-  __shared__ int s_bad;
+  __shared__ int s_bad, s_cnt;
   const int s = blockIdx.x;
+  if (smode[s] < 0) {
+    // automatic strategy: the reference's rule for a CUDA tensor (boxes.py:72, numel() > 20000 -> vanilla) sees the
+    // boxes that SURVIVED the filters (rpn.py:276-288, roi_heads.py:708-716 compact before batched_nms), so it is
+    // decided here from the number of valid boxes of the set, not on the host from the set's size
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    int c = 0;
+    for (int i = off[s] + threadIdx.x; i < off[s + 1]; i += blockDim.x) c += (!valid || valid[i]) ? 1 : 0;
+    if (c) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    if (threadIdx.x == 0) smode[s] = 4 * s_cnt > 20000 ? 2 : 1;
+    __syncthreads();
+  }
   if (smode[s] == 2) {
     if (threadIdx.x == 0) sgroup[s] = 1;
     return;
@@ -1259,8 +1272,9 @@ int nms_seg_t(const void* boxes, const void* scores, const int64_t* idxs, const 
       b.mode[j] = 0;
       if (j < b.count) {
         const long long ns = seg_offsets[base + j + 1] - seg_offsets[base + j];
-        // mode < 0: the reference's rule for a CUDA tensor, image by image (boxes.py:72)
-        b.mode[j] = (signed char)(!idxs ? 0 : (mode >= 0 ? mode : (4 * ns > 20000 ? 2 : 1)));
+        // mode < 0: the reference's rule for a CUDA tensor, set by set, decided on the device from the number of
+        // boxes that pass the filters (nms_seg_max_kernel)
+        b.mode[j] = (signed char)(!idxs ? 0 : (mode >= 0 ? mode : -1));
         const long long cb = (ns + kTile - 1) / kTile;
         mo += (ns * cb + 1) & ~1LL;  // 16-byte aligned segments: the scan stages rows with bulk copies
         ro += (int)cb;

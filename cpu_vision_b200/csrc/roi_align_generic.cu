@@ -130,22 +130,33 @@ __global__ void __launch_bounds__(kThreads) roi_align_bwd_generic_kernel(
   }
 }
 
-// poolers.py:73-84.  fp32 arithmetic in the order torch evaluates it on the
-// reference's CPU path: area = (x2-x1)*(y2-y1) (box_area after _upcast,
-// boxes.py:278-295), s = sqrt(area), floor(lvl0 + log2(s / s0) + eps) with a
-// true division, clamp, minus k_min.
-__global__ void fpn_level_map_kernel(const float* __restrict__ rois, long long K, int k_min,
-                                     int k_max, float s0, float lvl0, float eps,
-                                     int32_t* __restrict__ levels) {
+// poolers.py:73-84.  Arithmetic in the boxes' dtype (fp32, or fp64 for fp64 boxes) in the order torch evaluates it
+// on the reference's CPU path: area = (x2-x1)*(y2-y1) (box_area after _upcast, boxes.py:278-295), s = sqrt(area),
+// floor(lvl0 + log2(s / s0) + eps) with a true division, clamp, minus k_min.
+template <typename R> struct LvlMath;
+template <> struct LvlMath<float> {
+  static __device__ __forceinline__ float sqrt_(float v) { return sqrtf(v); }
+  static __device__ __forceinline__ float log2_(float v) { return log2f(v); }
+  static __device__ __forceinline__ float floor_(float v) { return floorf(v); }
+};
+template <> struct LvlMath<double> {
+  static __device__ __forceinline__ double sqrt_(double v) { return sqrt(v); }
+  static __device__ __forceinline__ double log2_(double v) { return log2(v); }
+  static __device__ __forceinline__ double floor_(double v) { return floor(v); }
+};
+template <typename R>
+__global__ void fpn_level_map_kernel(const R* __restrict__ rois, long long K, int k_min, int k_max, R s0, R lvl0,
+                                     R eps, int32_t* __restrict__ levels) {
   const long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (k >= K) return;
-  const float* r = rois + k * 5;
-  const float x1 = __ldg(r + 1), y1 = __ldg(r + 2), x2 = __ldg(r + 3), y2 = __ldg(r + 4);
-  const float area = __fmul_rn(__fsub_rn(x2, x1), __fsub_rn(y2, y1));
-  const float s = sqrtf(area);
-  float t = floorf(__fadd_rn(__fadd_rn(lvl0, log2f(__fdiv_rn(s, s0))), eps));
+  const R* r = rois + k * 5;
+  const R x1 = __ldg(r + 1), y1 = __ldg(r + 2), x2 = __ldg(r + 3), y2 = __ldg(r + 4);
+  const R area = Ar<R>::mul(Ar<R>::sub(x2, x1), Ar<R>::sub(y2, y1));
+  const R s = LvlMath<R>::sqrt_(area);
+  R t = LvlMath<R>::floor_(Ar<R>::add(Ar<R>::add(lvl0, LvlMath<R>::log2_(Ar<R>::div(s, s0))), eps));
   // clamp; a NaN (negative area) lands on k_min where torch's int cast is undefined
-  t = fminf(fmaxf(t, (float)k_min), (float)k_max);
+  t = t >= (R)k_min ? t : (R)k_min;
+  t = t <= (R)k_max ? t : (R)k_max;
   levels[k] = (int32_t)t - k_min;
 }
 template <typename T>
@@ -245,12 +256,14 @@ int roi_align_bwd_generic(const LevelArgs& lv, int dtype, const void* grad, cons
 int fpn_level_map(const void* rois, int dtype, long long K, int k_min, int k_max, int s0, int lvl0,
                   double eps, int32_t* levels, cudaStream_t st) {
   if (K == 0) return 0;
-  if (dtype == B200DET_F64)
-    return fail(B200DET_ENOSUP, "fpn_level_map: fp64 rois are not supported");
   const int th = 256;
   const int bl = (int)((K + th - 1) / th);
-  fpn_level_map_kernel<<<bl, th, 0, st>>>((const float*)rois, K, k_min, k_max, (float)s0, (float)lvl0,
-                                          (float)eps, levels);
+  if (dtype == B200DET_F64)
+    fpn_level_map_kernel<double><<<bl, th, 0, st>>>((const double*)rois, K, k_min, k_max, (double)s0, (double)lvl0,
+                                                    eps, levels);
+  else
+    fpn_level_map_kernel<float><<<bl, th, 0, st>>>((const float*)rois, K, k_min, k_max, (float)s0, (float)lvl0,
+                                                   (float)eps, levels);
   B200DET_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -208,7 +208,8 @@ def _segmented_oracle(b, s, i, off, thr, valid, mode, top_n):
         if i is None:
             keep = oracle.nms(b[sel], s[sel], thr)
         else:
-            m = mode if mode != "auto" else ("vanilla" if 4 * (off[k + 1] - off[k]) > 20000 else "trick")
+            # the reference's rule (boxes.py:72) sees the boxes AFTER the boxes[keep] compactions
+            m = mode if mode != "auto" else ("vanilla" if 4 * sel.numel() > 20000 else "trick")
             keep = oracle.batched_nms(b[sel], s[sel], i[sel], thr, m)
         keep = sel[keep]
         out.append(keep[:top_n] if top_n > 0 else keep)
@@ -248,6 +249,27 @@ def test_segmented_auto_mode_and_negative_coordinates(capi):
     i = torch.randint(0, 4, (6100,), generator=g)
     want = _segmented_oracle(b, s, i, off, 0.5, None, "auto", 0)
     got = capi.nms_segmented(b.to(DEV), s.to(DEV), i.to(DEV), off, 0.5)
+    for a, w in zip(got, want):
+        assert torch.equal(a.cpu(), w)
+
+
+def test_segmented_auto_mode_counts_the_surviving_boxes(capi):
+    """A set of 8000 candidates of which the filters keep 3500: the reference compacts first (rpn.py:276-288), so
+    batched_nms sees 14 000 elements and takes the coordinate trick; 8000 unfiltered candidates take the vanilla
+    strategy.  Negative coordinates make the two strategies differ, so the choice is visible in the result."""
+    g = torch.Generator().manual_seed(78)
+    n = 8000
+    off = [0, n, 2 * n]
+    b, s = make_boxes(g, 2 * n, span=120.0, lo=20.0, hi=60.0)
+    b = b - 100.0   # offsets idx * (max + 1) no longer separate the classes: the strategies disagree
+    i = torch.randint(0, 4, (2 * n,), generator=g)
+    valid = torch.zeros(2 * n, dtype=torch.bool)
+    valid[torch.randperm(n, generator=g)[:3500]] = True       # first set: 3500 survivors -> trick
+    valid[n:] = True                                          # second set: all 8000 -> vanilla
+    want = _segmented_oracle(b, s, i, off, 0.5, valid, "auto", 0)
+    other = _segmented_oracle(b, s, i, off, 0.5, valid, "vanilla", 0)
+    assert not torch.equal(want[0], other[0]), "the case must tell the strategies apart"
+    got = capi.nms_segmented(b.to(DEV), s.to(DEV), i.to(DEV), off, 0.5, valid=valid.to(DEV))
     for a, w in zip(got, want):
         assert torch.equal(a.cpu(), w)
 

@@ -124,7 +124,12 @@ def _pyramid_case(seed, images, per_img, ph, dtype=torch.float32):
     levels = oracle.fpn_level_map(rois, 2, 5)
     go = torch.randn(images * per_img, 256, ph, ph, generator=g).to(dtype)
     shapes = [(images, 256, h, w) for h, w in SHAPES]
-    want = oracle.msroi_align_backward(go.double(), rois.double(), levels, SCALES, shapes, ph, ph, 2, False)
+    # fp64 truth level by level (oracle.msroi_align_backward itself computes in fp32)
+    want = []
+    for l, (h, w) in enumerate(SHAPES):
+        sel = (levels == l).nonzero().flatten()
+        want.append(oracle.roi_align_backward(go[sel].double(), rois[sel].double(), SCALES[l], ph, ph, images, 256, h, w,
+                                              2, False))
     return rois, levels, go, shapes, want
 
 

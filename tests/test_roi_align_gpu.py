@@ -165,6 +165,28 @@ def test_fp64_matches_oracle(capi):
                                    rtol=1e-12, atol=1e-13)
 
 
+def test_fp64_pyramid_and_single_level_levels(capi):
+    """fp64 features through the FPN path: the level map runs in fp64 like LevelMapper on fp64 boxes
+    (poolers.py:73-84), and a one-level pyramid returns all-zero level ids (they are saved for the backward)."""
+    g = torch.Generator().manual_seed(15)
+    shapes, scales = [(24, 32), (12, 16)], [0.25, 0.125]
+    feats = [torch.randn(2, 4, h, w, generator=g, dtype=torch.float64) for h, w in shapes]
+    rois = rand_rois(g, 40, 2, 128.0, 96.0, lo=4.0).double()
+    lv = oracle.fpn_level_map(rois.float(), 2, 3)
+    want = torch.zeros(40, 4, 3, 3, dtype=torch.float64)
+    for l in range(2):
+        sel = (lv == l).nonzero().flatten()
+        want[sel] = oracle.roi_align_forward(feats[l], rois[sel], 3, 3, scales[l], 2, False)
+    out, levels = capi.msroi_align_forward([f.to(DEV) for f in feats], rois.to(DEV), scales, 3, 3, 2, False, k_min=2,
+                                           k_max=3)
+    assert torch.equal(levels.cpu().long(), lv)
+    torch.testing.assert_close(out.cpu(), want, rtol=1e-12, atol=1e-13)
+    out1, lv1 = capi.msroi_align_forward([feats[0].to(DEV)], rois.to(DEV), scales[:1], 3, 3, 2, False, k_min=2, k_max=2)
+    assert lv1.shape == (40,) and int(lv1.abs().sum()) == 0
+    torch.testing.assert_close(out1.cpu(), oracle.roi_align_forward(feats[0], rois, 3, 3, 0.25, 2, False),
+                               rtol=1e-12, atol=1e-13)
+
+
 def test_edge_rois(capi):
     """Malformed, out-of-image, zero-size and sub-pixel RoIs; empty inputs."""
     g = torch.Generator().manual_seed(2)
