@@ -11,6 +11,9 @@ Produces (all git-ignored; they travel to the GPU box with the gpurun snapshot):
                                      one g++ call per file).  This is the configuration INTEGRATION.md
                                      describes: schemas, Autograd and Autocast kernels come from the
                                      reference, `cpu_vision_b200` adds only the CUDA kernels.
+  baseline/_ref/test/                the reference's own test files for the path (test_ops.py, test_models.py, their
+                                     helpers and the pickled expectations), copied as they are: tests/test_dropin_gpu.py
+                                     runs them against the new CUDA kernels
   baseline/_ref/tvref_cuda.so        (--cuda) the reference's own cuda/roi_align_kernel.cu and
                                      cuda/nms_kernel.cu compiled unmodified for sm_100a: the stock GPU
                                      kernels as a reported comparison.  Loaded only by
@@ -63,7 +66,7 @@ def build_package(force=False):
     csrc, inc, abi, torch_lib = _flags()
     obj_dir = os.path.join(OUT, "obj")
     if os.path.exists(pkg):
-        shutil.rmtree(pkg)
+        _rmtree(pkg)
     os.makedirs(obj_dir, exist_ok=True)
     shutil.copytree(os.path.join(REF, "torchvision"), pkg,
                     ignore=shutil.ignore_patterns("csrc", "*.so", "__pycache__"))
@@ -85,7 +88,44 @@ def build_package(force=False):
                           ["-L" + torch_lib, "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_python",
                            "-Wl,-rpath," + torch_lib])
     shutil.rmtree(obj_dir)
+    _writable(pkg)
     return OUT
+
+
+def copy_tests(force=False):
+    """The reference's tests that pin the boundary, unmodified."""
+    dst = os.path.join(OUT, "test")
+    src = os.path.join(REF, "test")
+    if os.path.isdir(dst) and not force:
+        return dst
+    if not os.path.isdir(src):
+        return dst if os.path.isdir(dst) else None
+    if os.path.isdir(dst):
+        _rmtree(dst)
+    os.makedirs(dst)
+    for f in ("test_ops.py", "test_models.py", "common_utils.py", "conftest.py", "_utils_internal.py",
+              "optests_failures_dict.json", "common_extended_utils.py"):
+        if os.path.exists(os.path.join(src, f)):
+            shutil.copy(os.path.join(src, f), os.path.join(dst, f))
+    shutil.copytree(os.path.join(src, "expect"), os.path.join(dst, "expect"))
+    os.makedirs(os.path.join(dst, "assets"))
+    for f in ("encode_jpeg",):  # (assets the model tests open)
+        p = os.path.join(src, "assets", f)
+        if os.path.isdir(p):
+            shutil.copytree(p, os.path.join(dst, "assets", f))
+    _writable(dst)
+    return dst
+
+
+def _writable(path):
+    for root, dirs, files in os.walk(path):
+        for n in dirs + files:
+            os.chmod(os.path.join(root, n), 0o755 if n in dirs else 0o644)
+
+
+def _rmtree(path):
+    _writable(path)
+    shutil.rmtree(path)
 
 
 def build_stock_cuda(force=False):
@@ -111,6 +151,7 @@ def build_stock_cuda(force=False):
 def main():
     force = "--force" in sys.argv
     print("package:", build_package(force))
+    print("reference tests:", copy_tests(force))
     if "--cuda" in sys.argv:
         print("stock cuda kernels:", build_stock_cuda(force))
 

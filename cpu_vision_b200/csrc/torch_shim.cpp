@@ -14,6 +14,7 @@
 //
 // No kernel code here: every op forwards raw pointers to libb200det.so.
 #include <ATen/ATen.h>
+#include <ATen/autocast_mode.h>
 #include <ATen/core/dispatch/Dispatcher.h>
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
@@ -218,6 +219,45 @@ at::Tensor nms_cuda(const at::Tensor& dets, const at::Tensor& scores, double iou
   at::cuda::CUDAGuard device_guard(dets.device());
   if (dets.numel() == 0) return at::empty({0}, dets.options().dtype(at::kLong));
   return run_nms(dets, scores, nullptr, iou_threshold, 0);
+}
+
+// ---- Autocast ------------------------------------------------------------------
+// The reference's wrappers (csrc/ops/autocast/roi_align_kernel.cpp:12-31, autocast/nms_kernel.cpp:12-23) cast
+// every argument to fp32, i.e. make an fp32 copy of the whole feature map, run the fp32 kernel and cast the
+// result back.  The sm_100a kernels read fp16 / bf16 natively (fp32 arithmetic and accumulation, widened on load),
+// which computes exactly ref_fp32(x.float(), rois.float()).to(x.dtype) without the copy.  So under
+// torch.autocast("cuda") 16-bit features stay as they are, RoIs go to fp32 like in the reference, and fp32
+// features take the fp32 path unchanged; the result has the input's dtype (test/test_ops.py:493-508).  These
+// kernels are registered for the Autocast (CUDA) key and replace the reference's when its _C is loaded too.
+at::Tensor roi_align_autocast_cuda(const at::Tensor& input, const at::Tensor& rois, double spatial_scale,
+                                   int64_t pooled_height, int64_t pooled_width, int64_t sampling_ratio,
+                                   bool aligned) {
+  c10::impl::ExcludeDispatchKeyGuard no_autocast(c10::DispatchKey::Autocast);
+  static auto op = c10::Dispatcher::singleton()
+                       .findSchemaOrThrow("torchvision::roi_align", "")
+                       .typed<at::Tensor(const at::Tensor&, const at::Tensor&, double, int64_t, int64_t, int64_t, bool)>();
+  const auto it = input.scalar_type();
+  const at::Tensor rois32 = at::autocast::cached_cast(at::kFloat, rois, c10::DeviceType::CUDA);
+  if (input.is_cuda() && (it == at::kHalf || it == at::kBFloat16))
+    return op.call(input, rois32, spatial_scale, pooled_height, pooled_width, sampling_ratio, aligned);
+  return op
+      .call(at::autocast::cached_cast(at::kFloat, input, c10::DeviceType::CUDA), rois32, spatial_scale,
+            pooled_height, pooled_width, sampling_ratio, aligned)
+      .to(it);
+}
+
+at::Tensor nms_autocast_cuda(const at::Tensor& dets, const at::Tensor& scores, double iou_threshold) {
+  c10::impl::ExcludeDispatchKeyGuard no_autocast(c10::DispatchKey::Autocast);
+  static auto op = c10::Dispatcher::singleton()
+                       .findSchemaOrThrow("torchvision::nms", "")
+                       .typed<at::Tensor(const at::Tensor&, const at::Tensor&, double)>();
+  const auto dt = dets.scalar_type();
+  // fp16 / bf16 boxes and scores of one dtype run natively: IoU in fp32 on the widened values, the same order of
+  // scores -- what the fp32 cast would compute
+  if (dets.is_cuda() && dt == scores.scalar_type() && (dt == at::kHalf || dt == at::kBFloat16))
+    return op.call(dets, scores, iou_threshold);
+  return op.call(at::autocast::cached_cast(at::kFloat, dets, c10::DeviceType::CUDA),
+                 at::autocast::cached_cast(at::kFloat, scores, c10::DeviceType::CUDA), iou_threshold);
 }
 
 // ---- b200det::batched_nms -------------------------------------------------------
@@ -615,6 +655,9 @@ struct Registrar {
     g_libs.back()->impl("_ps_roi_pool_backward", TORCH_FN(ps_roi_pool_backward_cuda));
     g_libs.back()->impl("ps_roi_align", TORCH_FN(ps_roi_align_forward_cuda));
     g_libs.back()->impl("_ps_roi_align_backward", TORCH_FN(ps_roi_align_backward_cuda));
+    g_libs.emplace_back(new torch::Library(torch::Library::IMPL, "torchvision", c10::DispatchKey::Autocast, __FILE__, __LINE__));
+    g_libs.back()->impl("roi_align", TORCH_FN(roi_align_autocast_cuda));
+    g_libs.back()->impl("nms", TORCH_FN(nms_autocast_cuda));
   }
 };
 Registrar g_registrar;
