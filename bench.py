@@ -40,12 +40,12 @@ C = 256
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=30)
+    p.add_argument("--steps", type=int, default=200)  # ~0.3 s timed region at 1.6 ms per step
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--workload", default="cfg3_fp32", choices=["cfg3_fp32", "cfg3_bf16"])
     p.add_argument("--no-extras", action="store_true", help="skip e2e / cpu_baseline / secondary legs")
-    p.add_argument("--gather", action="store_true", help="also time the NCCL all-gather of pooled features")
+    p.add_argument("--gather", action="store_true", help="(kept for compatibility: the cfg4 exchange now always runs at N > 1)")
     return p.parse_args()
 
 
@@ -191,7 +191,16 @@ def run_reference(args, rank):
     batch, per_img, ph = 16, 512, 14
     feats = [torch.randn(batch, C, h, w, generator=gen) for h, w in SHAPES]
     rois = make_rois(gen, batch, per_img, 16.0, 800.0, "cpu")
-    stride = 8  # 1024 of the 8192 RoIs per step: a few seconds of CPU work per step
+    # the whole batch per step (a sample would spread the reference's per-call cost -- allocating and zero-filling
+    # the 1.18 GB gradient like its at::zeros -- over fewer RoIs and under-count the CPU); ~3 s of CPU work per step
+    stride = 1
+    torch.set_num_threads(threads)  # torchrun exports OMP_NUM_THREADS=1: the zero fills would run on one core
+    try:
+        import oracle
+
+        oracle.lib("ref").tvref_set_num_threads(threads)
+    except Exception:
+        pass
     k_s = len(range(0, rois.shape[0], stride))
     gsel = torch.randn(k_s, C, ph, ph, generator=gen)  # upstream gradient of the sampled RoIs only
 
@@ -204,13 +213,15 @@ def run_reference(args, rank):
             break
     ms = 1e3 * sum(times) / len(times)
     val = n / (ms / 1e3)
-    sample = f"{n} of {rois.shape[0]} RoIs (every {stride}th) of the cfg3 batch, fwd+bwd, 4 levels"
+    sample = (f"all {n} RoIs of the cfg3 batch per step, fwd+bwd, 4 levels, {threads} host threads (forward sharded "
+              "over RoIs, backward over images: <= 16 threads)")
     line = {
         "impl": "reference", "metric": "roi_align_fwd_bwd_rois_per_s", "value": val, "unit": "RoIs/s",
         "n_gpus": args.gpus, "steps": len(times), "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config("cfg3_fp32"),
-        "cpu_baseline": {"value": val, "unit": "RoIs/s", "cores": threads, "kind": kind, "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "RoIs/s", "cores": threads, "kind": kind, "sample": sample,
+                         "nms": cpu_nms_leg()},
         "e2e": {"value": val, "unit": "RoIs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -342,9 +353,17 @@ def run_b200(args, rank, world, local):
         line["e2e"] = e2e_leg(capi, feats, rois, grad, levels, shapes, ph, dtype, local, world, K, dist)
         if rank == 0 and world == 1:
             line["cpu_baseline"] = cpu_leg(feats, rois, grad, ph)
+        del feats, grad, gfeats, out
+        torch.cuda.empty_cache()
+        cfg4 = cfg4_leg(capi, dev, rank, world, dist, peak)
+        if world > 1:
+            line["cfg4"] = cfg4["cfg4"]
+            line["allgather"] = cfg4["allgather"]
+        if rank == 0 and world == 1:
             line["secondary"] = secondary_legs(capi, dev, peak)
-        if world > 1 and args.gather:
-            line["allgather"] = gather_leg(out, world, dist)
+            line["secondary"]["cfg4_64img_x_2000"] = cfg4["cfg4"]
+            line["secondary"]["stock_cuda_kernels"] = subprocess_leg("stock_cuda_bench.py", "tvref_cuda.so")
+            line["secondary"]["cfg5_model"] = subprocess_leg("cfg5_model_bench.py", os.path.join("torchvision", "_C.so"))
     if rank == 0:
         print(json.dumps(line), flush=True)
 
@@ -386,16 +405,51 @@ def e2e_leg(capi, feats, rois, grad, levels, shapes, ph, dtype, local, world, K,
             "api": "b200det_msroi_align_forward_host + b200det_msroi_align_backward_host (pinned host buffers)"}
 
 
+def cpu_nms_leg():
+    """cfg2 on the host: the reference's CPU nms kernel (cpu/nms_kernel.cpp:9-77, one thread by construction)
+    through its batched_nms strategy rule for a CPU tensor (boxes.py:72: numel > 4000 -> one nms per class,
+    boxes.py:98-112), and plain nms of the same 5000 boxes."""
+    import oracle
+
+    impl = "ref" if oracle.have_ref() else "oracle"
+    gen = torch.Generator().manual_seed(1234 + 2)
+    n = 5000
+    xy = torch.rand(n, 2, generator=gen) * 1000
+    boxes = torch.cat([xy, xy + torch.rand(n, 2, generator=gen) * 200 + 10], 1)
+    scores = torch.randperm(n, generator=gen).float() / n
+    idxs = torch.randint(0, 80, (n,), generator=gen)
+
+    def vanilla():
+        keep = torch.zeros(n, dtype=torch.bool)
+        for c in torch.unique(idxs):
+            sel = torch.where(idxs == c)[0]
+            keep[sel[oracle.nms(boxes[sel], scores[sel], 0.5, impl=impl)]] = True
+        k = torch.where(keep)[0]
+        return k[scores[k].sort(descending=True)[1]]
+
+    def best(fn, reps):
+        b = float("inf")
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            b = min(b, time.perf_counter() - t0)
+        return b
+
+    tb, tn = best(vanilla, 5), best(lambda: oracle.nms(boxes, scores, 0.5, impl=impl), 5)
+    return {"batched_nms_5000x80_ms": tb * 1e3, "batched_nms_boxes_per_s": n / tb, "nms_5000_ms": tn * 1e3,
+            "nms_boxes_per_s": n / tn, "cores": 1, "kind": "reference" if impl == "ref" else "port",
+            "sample": "cfg2 whole (5000 boxes x 80 classes, IoU 0.5), best of 5"}
+
+
 def cpu_leg(feats, rois, grad, ph):
     threads = os.cpu_count() or 1
-    stride = 8
-    sel = torch.arange(0, rois.shape[0], stride, device=rois.device)
+    torch.set_num_threads(threads)
     fc = [f.float().cpu().contiguous() for f in feats]
-    sec, n, kind = cpu_reference_sample(fc, rois.cpu(), grad[sel].float().cpu().contiguous(), ph, stride, threads,
-                                        repeats=2)
+    sec, n, kind = cpu_reference_sample(fc, rois.cpu(), grad.float().cpu().contiguous(), ph, 1, threads, repeats=2)
     return {"value": n / sec, "unit": "RoIs/s", "cores": threads, "kind": kind, "seconds": sec,
-            "sample": f"{n} of {rois.shape[0]} RoIs (every {stride}th) of the same batch, fwd+bwd, best of 2; "
-                      "forward sharded over RoIs, backward over images (<=16 threads)"}
+            "sample": f"all {n} RoIs of the same batch, fwd+bwd, best of 2; forward sharded over RoIs, backward "
+                      "over images (<=16 threads)",
+            "nms": cpu_nms_leg()}
 
 
 def secondary_legs(capi, dev, peak):
@@ -544,6 +598,147 @@ def secondary_legs(capi, dev, peak):
     res["cfg5_roi_heads_postprocess_64img"] = {
         "instances_per_image": P_ * (C_ - 1), "postprocess_detections_ms": f1b_ms,
         "instances_per_s": B * P_ * (C_ - 1) / (f1b_ms / 1e3), "detections": det_n}
+    return res
+
+
+def subprocess_leg(script, needs):
+    """Legs that need the reference's package (baseline/_ref) run in a process of their own: it must not be
+    imported next to the stand-alone product (both define torchvision:: schemas)."""
+    import subprocess
+
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.exists(os.path.join(ref, needs)):
+        return {"unavailable": f"baseline/_ref/{needs} not built (python baseline/build_ref.py --cuda)"}
+    env = dict(os.environ)
+    env["PYTHONPATH"] = os.pathsep.join([ref, ROOT, env.get("PYTHONPATH", "")])
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    try:
+        p = subprocess.run([sys.executable, os.path.join(ROOT, "baseline", script)], env=env, capture_output=True,
+                           text=True, timeout=900)
+        if p.returncode != 0:
+            return {"unavailable": (p.stderr or p.stdout)[-300:]}
+        return json.loads(p.stdout.strip().splitlines()[-1])
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": repr(e)[:300]}
+
+
+def cfg4_leg(capi, dev, rank, world, dist, peak):
+    """BASELINE.json configs[3]: 64 images x 2000 RoIs (7x7, 4 FPN levels, fp32), images split 64 / N per rank
+    (STRONG scaling).  Forward written straight into this rank's slice of the gather buffer, backward, then the
+    exchange north_star names: an NCCL all-gather of the pooled features [128000, 256, 7, 7] (6.42 GB) and of the
+    kept indices of a per-rank batched_nms.  The all-gather is also pipelined behind the forward (image chunks:
+    chunk c is pooled while chunk c - 1 is on the wire; the buffer is then ordered chunk, rank, RoI)."""
+    from cpu_vision_b200 import sharding
+
+    B, per_img, ph = 64, 2000, 7
+    lo, hi = sharding.image_block(B, rank, world)
+    nb = hi - lo
+    gen = torch.Generator(device=dev).manual_seed(1234 + 4 + rank)
+    feats = [torch.randn(nb, C, h, w, generator=gen, device=dev).contiguous(memory_format=torch.channels_last)
+             for h, w in SHAPES]
+    rois = make_rois(gen, nb, per_img, 16.0, 800.0, dev)
+    K = nb * per_img
+    grad = torch.randn(K, C, ph, ph, generator=gen, device=dev).contiguous(memory_format=torch.channels_last)
+    gfeats = [torch.empty_like(f) for f in feats]
+    shapes = [(nb, C, h, w) for h, w in SHAPES]
+    full, mine = sharding.gather_buffer(K, (C, ph, ph), torch.float32, dev, rank, world, torch.channels_last)
+    levels = capi.fpn_level_map(rois, 2, 5)
+    sync = torch.cuda.synchronize
+
+    def timed(fn, iters=5, warm=2):
+        for _ in range(warm):
+            fn()
+        if world > 1:
+            dist.barrier()
+        sync()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        b.synchronize()
+        ms = a.elapsed_time(b) / iters
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms
+
+    fwd = lambda: capi.msroi_align_forward(feats, rois, SCALES, ph, ph, 2, False, levels=levels, out=mine)
+    bwd = lambda: capi.msroi_align_backward(grad, rois, levels, SCALES, shapes, ph, ph, 2, False, layout=capi.NHWC,
+                                            outs=gfeats)
+    f_ms, b_ms = timed(fwd), timed(bwd)
+    fb = sum(f.numel() for f in feats) * 4
+    ob = K * C * ph * ph * 4
+    res = {"cfg4": {
+        "images": B, "rois": B * per_img, "images_per_rank": nb, "scaling": "strong", "fwd_ms": f_ms, "bwd_ms": b_ms,
+        "bwd_rois_per_s": B * per_img / (b_ms / 1e3), "fwd_bwd_rois_per_s": B * per_img / ((f_ms + b_ms) / 1e3),
+        "bwd_frac_of_hbm": (fb + ob + K * 20) / (b_ms / 1e3) / 1e9 / peak,
+        "fwd_frac_of_hbm": (fb + ob + K * 20) / (f_ms / 1e3) / 1e9 / peak}}
+    if world == 1:
+        return res
+    # --- the exchange
+    ag_ms = timed(lambda: dist.all_gather_into_tensor(full, mine), iters=3, warm=1)
+    del grad, gfeats
+    torch.cuda.empty_cache()
+    tmp_in = torch.empty_like(mine)
+    tmp_out = torch.empty_like(full)
+    plain_ms = timed(lambda: dist.all_gather_into_tensor(tmp_out, tmp_in), iters=3, warm=1)
+    del tmp_in, tmp_out
+    recv = (world - 1) * mine.numel() * 4
+    # kept indices: one batched_nms per rank (cfg2 shape), gathered as (count, padded int64[capacity])
+    n = 5000
+    xy = torch.rand(n, 2, generator=gen, device=dev) * 1000
+    boxes = torch.cat([xy, xy + torch.rand(n, 2, generator=gen, device=dev) * 200 + 10], 1)
+    scores = torch.randperm(n, generator=gen, device=dev).float() / n
+    idxs = torch.randint(0, 80, (n,), generator=gen, device=dev)
+    keep = capi.batched_nms(boxes, scores, idxs, 0.5)
+    cnt = torch.tensor([keep.numel()], device=dev)
+    kept_ms = timed(lambda: sharding.all_gather_keep(keep, cnt, n), iters=3, warm=1)
+    # pipelined: chunk c pooled while chunk c - 1 is gathered (NCCL's stream waits for the kernels enqueued before
+    # the call; async_op returns at once, so the next chunk's kernels overlap the transfer)
+    chunks = min(4, nb)
+    ipc = nb // chunks
+    chunks = nb // ipc
+    Kc = ipc * per_img
+    piped = torch.empty((chunks * world * Kc, C, ph, ph), dtype=torch.float32, device=dev,
+                        memory_format=torch.channels_last)
+    parts = []
+    for c in range(chunks):
+        r = rois[c * Kc:(c + 1) * Kc].clone()
+        r[:, 0] -= c * ipc
+        parts.append(([f[c * ipc:(c + 1) * ipc] for f in feats], r, levels[c * Kc:(c + 1) * Kc].contiguous(),
+                      piped[(c * world) * Kc:((c + 1) * world) * Kc], piped[(c * world + rank) * Kc:(c * world + rank + 1) * Kc]))
+
+    def pipelined():
+        hs = []
+        for fs, r, lv, dst, my in parts:
+            capi.msroi_align_forward(fs, r, SCALES, ph, ph, 2, False, levels=lv, out=my)
+            hs.append(dist.all_gather_into_tensor(dst, my, async_op=True))
+        for h in hs:
+            h.wait()
+
+    def sequential():
+        for fs, r, lv, dst, my in parts:
+            capi.msroi_align_forward(fs, r, SCALES, ph, ph, 2, False, levels=lv, out=my)
+        torch.cuda.current_stream().synchronize()
+        for fs, r, lv, dst, my in parts:
+            dist.all_gather_into_tensor(dst, my)
+
+    pipe_ms = timed(pipelined, iters=3, warm=1)
+    seq_ms = timed(sequential, iters=3, warm=1)
+    res["allgather"] = {
+        "what": "pooled features of cfg4, [128000, 256, 7, 7] fp32 = 6.42 GB, all_gather_into_tensor in place "
+                "(the forward wrote this rank's slice of the buffer)",
+        "ms": ag_ms, "bytes_received_per_gpu": recv, "recv_GBps_per_gpu": recv / (ag_ms / 1e3) / 1e9,
+        "nccl_plain_allgather_same_size_ms": plain_ms, "nccl_plain_recv_GBps_per_gpu": recv / (plain_ms / 1e3) / 1e9,
+        "frac_of_nccl_plain": plain_ms / ag_ms,
+        "kept_indices_allgather_ms": kept_ms, "kept_indices_bytes_per_rank": (n + 1) * 8,
+        "forward_then_gather_ms": seq_ms, "pipelined_forward_gather_ms": pipe_ms, "chunks": chunks,
+        "overlap_frac": (seq_ms - pipe_ms) / max(min(f_ms, ag_ms), 1e-9),
+        "limiter": "the all-gather: every GPU receives (N-1)/N of 6.42 GB over NVLink while the local kernels "
+                   "take fwd_ms + bwd_ms"}
     return res
 
 
