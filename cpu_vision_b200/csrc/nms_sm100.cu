@@ -164,6 +164,28 @@ __global__ void nms_gather_kernel(const T* __restrict__ boxes, const int64_t* __
 // device-wide radix sort costs 6 launches of 3-11 us for 5000 keys and prepare / max / gather three more;
 // this is one launch.  Padding keys sort last (0xffffffff is the lowest float in radix order; a real key
 // with that bit pattern still precedes the padding because the sort is stable).
+// Programmatic dependent launch (sm_90+): the three launches of a small set (front end, IoU mask, scan) depend on
+// one another, so the 5-10 us between them were launch latency, a third of the call.  A kernel that calls
+// launch_dependents lets the next launch of the stream be scheduled at once; its CTAs sit in griddepcontrol.wait
+// until the whole previous grid has finished and its writes are visible, then start without a launch gap.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 constexpr int kSortThreads = 1024, kSortItems = 8, kSortMax = kSortThreads * kSortItems;
 
 template <typename T>
@@ -174,6 +196,7 @@ __global__ void __launch_bounds__(kSortThreads) nms_front_small_kernel(
   __shared__ typename Sort::TempStorage tmp;
   __shared__ float red[32];
   __shared__ float s_max;
+  pdl_launch_dependents();  // one CTA: the mask grid can take its places on the other SMs now
   const int tid = threadIdx.x;
   float k[kSortItems];
   int32_t v[kSortItems];
@@ -427,6 +450,8 @@ __global__ void __launch_bounds__(kTile) nms_mask_kernel(int n, float thr,
                                                          const BoxT* __restrict__ boxes,
                                                          const int32_t* __restrict__ cls,
                                                          u64* __restrict__ mask) {
+  pdl_launch_dependents();
+  pdl_wait();  // (before the early exit too: the grid must not complete before its predecessor has)
   const int row_start = blockIdx.y, col_group = blockIdx.x;
   if (row_start > col_group * kColTiles + kColTiles - 1) return;
   mask_tiles<BoxT>(n, thr, boxes, cls, mask, row_start, col_group);
@@ -734,6 +759,7 @@ __device__ __forceinline__ void scan_smem_body(
 __global__ void __launch_bounds__(kSmemThreads) nms_scan_smem_kernel(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
     int64_t* __restrict__ keep, int64_t* __restrict__ num_keep) {
+  pdl_wait();
   scan_smem_body(mask, n, col_blocks, order, keep, num_keep, nullptr, 0);
 }
 
@@ -798,6 +824,7 @@ __device__ __forceinline__ void scan_body(
 __global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
     int64_t* __restrict__ keep, int64_t* __restrict__ num_keep) {
+  pdl_wait();
   scan_body(mask, n, col_blocks, order, keep, num_keep, nullptr, 0);
 }
 
@@ -895,18 +922,20 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
                                             (BoxT*)L.sorted, mode == 2 ? L.cls : nullptr);
   }
   dim3 grid((col_blocks + kColTiles - 1) / kColTiles, col_blocks);
-  nms_mask_kernel<BoxT><<<grid, kTile, 0, st>>>((int)n, (float)thr, (const BoxT*)L.sorted,
-                                               mode == 2 ? L.cls : nullptr, L.mask);
+  B200DET_CUDA_OK(launch_pdl(nms_mask_kernel<BoxT>, grid, dim3(kTile), 0, st, (int)n, (float)thr, (const BoxT*)L.sorted,
+                             (const int32_t*)(mode == 2 ? L.cls : nullptr), L.mask));
   if (col_blocks <= kSmemBlocks) {
     const size_t smem = ((size_t)(kRowGroups + 1) * col_blocks + 1 + kDiagRing * kTile + (size_t)2 * kTile * col_blocks) * sizeof(u64);
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    nms_scan_smem_kernel<<<1, kSmemThreads, smem, st>>>(L.mask, (int)n, col_blocks, L.order, keep, num_keep);
+    B200DET_CUDA_OK(launch_pdl(nms_scan_smem_kernel, dim3(1), dim3(kSmemThreads), smem, st, (const u64*)L.mask, (int)n,
+                               col_blocks, (const int32_t*)L.order, keep, num_keep));
   } else {
     const size_t smem = (size_t)col_blocks * 16;
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    nms_scan_kernel<<<1, kScanThreads, smem, st>>>(L.mask, (int)n, col_blocks, L.order, keep, num_keep);
+    B200DET_CUDA_OK(launch_pdl(nms_scan_kernel, dim3(1), dim3(kScanThreads), smem, st, (const u64*)L.mask, (int)n,
+                               col_blocks, (const int32_t*)L.order, keep, num_keep));
   }
   B200DET_CUDA_OK(cudaGetLastError());
   return 0;
