@@ -85,52 +85,116 @@ __device__ __forceinline__ void build_y(const RoiGeom<float>& g, int H, int row_
   }
 }
 
+// ---- the lane's CH channels of one feature pixel ---------------------------------------------
+// as loaded (float4 / 32-bit words: ptxas uses the loaded registers in place, with LaneVec's 64-bit raw words it
+// copied them first) and as packed fp32 pairs for the sm_100 intrinsics __ffma2_rn / __fmul2_rn
+template <typename T, int CH> struct PixVec;
+template <int CH> struct PixVec<float, CH> {
+  struct raw { float4 v[CH / 4]; };
+  static __device__ __forceinline__ void ld(raw& r, const float* p) {
+#pragma unroll
+    for (int h = 0; h < CH / 4; ++h) r.v[h] = __ldg(reinterpret_cast<const float4*>(p + 128 * h));
+  }
+  static __device__ __forceinline__ void f2(const raw& r, float2 (&o)[CH / 2]) {
+#pragma unroll
+    for (int h = 0; h < CH / 4; ++h) {
+      o[2 * h] = make_float2(r.v[h].x, r.v[h].y);
+      o[2 * h + 1] = make_float2(r.v[h].z, r.v[h].w);
+    }
+  }
+  static __device__ __forceinline__ void st(float* p, const float2 (&v)[CH / 2]) {
+#pragma unroll
+    for (int h = 0; h < CH / 4; ++h)
+      __stcs(reinterpret_cast<float4*>(p + 128 * h), make_float4(v[2 * h].x, v[2 * h].y, v[2 * h + 1].x, v[2 * h + 1].y));
+  }
+};
+template <typename T> struct Cvt2;
+template <> struct Cvt2<__nv_bfloat16> {
+  static __device__ __forceinline__ float2 widen(unsigned u) {
+    return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
+  }
+  static __device__ __forceinline__ unsigned narrow(float2 v) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+    return *reinterpret_cast<const unsigned*>(&h);
+  }
+};
+template <> struct Cvt2<__half> {
+  static __device__ __forceinline__ float2 widen(unsigned u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); }
+  static __device__ __forceinline__ unsigned narrow(float2 v) {
+    const __half2 h = __floats2half2_rn(v.x, v.y);
+    return *reinterpret_cast<const unsigned*>(&h);
+  }
+};
+template <typename T, int CH> struct PixVec {   // 16-bit elements: CH * 2 contiguous bytes per lane
+  struct raw { unsigned u[CH / 2]; };
+  static __device__ __forceinline__ void ld(raw& r, const T* p) {
+    if (CH == 8) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+      r.u[0] = v.x; r.u[1] = v.y; r.u[CH / 2 - 2] = v.z; r.u[CH / 2 - 1] = v.w;
+    } else {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+      r.u[0] = v.x; r.u[1] = v.y;
+    }
+  }
+  static __device__ __forceinline__ void f2(const raw& r, float2 (&o)[CH / 2]) {
+#pragma unroll
+    for (int i = 0; i < CH / 2; ++i) o[i] = Cvt2<T>::widen(r.u[i]);
+  }
+  static __device__ __forceinline__ void st(T* p, const float2 (&v)[CH / 2]) {
+    if (CH == 8)
+      __stcs(reinterpret_cast<uint4*>(p), make_uint4(Cvt2<T>::narrow(v[0]), Cvt2<T>::narrow(v[1]),
+                                                      Cvt2<T>::narrow(v[CH / 2 - 2]), Cvt2<T>::narrow(v[CH / 2 - 1])));
+    else
+      __stcs(reinterpret_cast<uint2*>(p), make_uint2(Cvt2<T>::narrow(v[0]), Cvt2<T>::narrow(v[1])));
+  }
+};
+
 // ---- one pooled row -----------------------------------------------------------------------
 template <typename T, int CH, int SR, int NR>
 __device__ __forceinline__ void sweep_row(const FwdTables& tb, const T* __restrict__ base, T* __restrict__ o,
                                           int ph, int C, int SX) {
-  using LV = LaneVec<T, CH>;
+  using PV = PixVec<T, CH>;
   constexpr int H2 = CH / 2;
   const T* rp[NR];
-  f32x2 wv[NR];
+  float wv[NR];
 #pragma unroll
   for (int r = 0; r < NR; ++r) {
     rp[r] = base + tb.y_off[ph][r];
-    const float w = tb.y_w[ph][r];
-    wv[r] = pack2(w, w);
+    wv[r] = tb.y_w[ph][r];
   }
-  typename LV::raw A[NR], B[NR];
-  f32x2 X[H2], Y[H2], acc[H2];
+  typename PV::raw A[NR], B[NR];
+  float2 X[H2], Y[H2], acc[H2];
 #pragma unroll
-  for (int i = 0; i < H2; ++i) { X[i] = 0ull; Y[i] = 0ull; acc[i] = 0ull; }
+  for (int i = 0; i < H2; ++i) { X[i] = make_float2(0.f, 0.f); Y[i] = X[i]; acc[i] = X[i]; }
 
   // v = sum_r w_r * buf[r]; as soon as a row of `buf` is consumed its registers
   // are refilled with the same row of the column two events ahead (offset co2)
-  auto vertical_refill = [&](typename LV::raw (&buf)[NR], f32x2 (&v)[H2], int co2) {
-    f32x2 t[H2];
+  auto vertical_refill = [&](typename PV::raw (&buf)[NR], float2 (&v)[H2], int co2) {
+    float2 t[H2];
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
-      LV::pairs(buf[r], t);
+      PV::f2(buf[r], t);
+      const float2 w2 = make_float2(wv[r], wv[r]);
 #pragma unroll
-      for (int i = 0; i < H2; ++i) v[i] = (r == 0) ? mul2(wv[0], t[i]) : fma2(wv[r], t[i], v[i]);
-      buf[r] = LV::ld(rp[r] + co2);
+      for (int i = 0; i < H2; ++i) v[i] = (r == 0) ? __fmul2_rn(w2, t[i]) : __ffma2_rn(w2, t[i], v[i]);
+      PV::ld(buf[r], rp[r] + co2);
     }
   };
   int j = 0;
   // samples j .. end-1 read the window (lo, hi); a bin is stored when its last sample is done
-  auto samples = [&](int end, const f32x2 (&lo)[H2], const f32x2 (&hi)[H2]) {
+  auto samples = [&](int end, const float2 (&lo)[H2], const float2 (&hi)[H2]) {
     for (; j < end; ++j) {
       const float4 s = tb.x.samp[j];
       if (__float_as_int(s.z)) {
-        const f32x2 hx = pack2(s.x, s.x), lx = pack2(s.y, s.y);
+        const float2 hx = make_float2(s.x, s.x), lx = make_float2(s.y, s.y);
 #pragma unroll
-        for (int i = 0; i < H2; ++i) acc[i] = fma2(lx, hi[i], fma2(hx, lo[i], acc[i]));
+        for (int i = 0; i < H2; ++i) acc[i] = __ffma2_rn(lx, hi[i], __ffma2_rn(hx, lo[i], acc[i]));
       }
       if (SR == 1 || (j & 1)) {
-        LV::st(o, acc);
+        PV::st(o, acc);
         o += C;
 #pragma unroll
-        for (int i = 0; i < H2; ++i) acc[i] = 0ull;
+        for (int i = 0; i < H2; ++i) acc[i] = make_float2(0.f, 0.f);
       }
     }
   };
@@ -141,9 +205,9 @@ __device__ __forceinline__ void sweep_row(const FwdTables& tb, const T* __restri
     // colofs[] is padded with two copies of its last entry, so the refills past the
     // end re-read a column that is already in L1 instead of branching
 #pragma unroll
-    for (int r = 0; r < NR; ++r) A[r] = LV::ld(rp[r] + tb.x.colofs[0]);
+    for (int r = 0; r < NR; ++r) PV::ld(A[r], rp[r] + tb.x.colofs[0]);
 #pragma unroll
-    for (int r = 0; r < NR; ++r) B[r] = LV::ld(rp[r] + tb.x.colofs[1]);
+    for (int r = 0; r < NR; ++r) PV::ld(B[r], rp[r] + tb.x.colofs[1]);
     int e = 0;
     while (true) {
       // event e sits in A and becomes X: window = (lo Y, hi X)
@@ -186,10 +250,10 @@ __global__ void __launch_bounds__(128, sizeof(T) == 2 ? 5 : 4) roi_align_fwd_sm1
       case 3: if (SR == 2) sweep_row<T, CH, SR, 3>(tb, base, o, ph, C, SX); break;
       case 4: if (SR == 2) sweep_row<T, CH, SR, 4>(tb, base, o, ph, C, SX); break;
       default: {  // every y sample of the row is empty: the bins are zero
-        f32x2 z[CH / 2];
+        float2 z[CH / 2];
 #pragma unroll
-        for (int i = 0; i < CH / 2; ++i) z[i] = 0ull;
-        for (int pw = 0; pw < PW; ++pw) LaneVec<T, CH>::st(o + (long long)pw * C, z);
+        for (int i = 0; i < CH / 2; ++i) z[i] = make_float2(0.f, 0.f);
+        for (int pw = 0; pw < PW; ++pw) PixVec<T, CH>::st(o + (long long)pw * C, z);
       }
     }
   }
