@@ -108,19 +108,19 @@ __device__ __forceinline__ int lane_elem_channel(int i) {
 
 template <typename T, int CH, bool VEC> struct GBuf;
 template <typename T, int CH> struct GBuf<T, CH, true> {   // unit channel stride: vector loads, converted on use
-  typename LaneVec<T, CH>::raw r;
-  __device__ __forceinline__ void load(const T* p, long long) { r = LaneVec<T, CH>::ld_stream(p); }
-  __device__ __forceinline__ void get(f32x2 (&v)[CH / 2]) const { LaneVec<T, CH>::pairs(r, v); }
+  typename PixVec<T, CH>::raw r;
+  __device__ __forceinline__ void load(const T* p, long long) { PixVec<T, CH>::ld_stream(r, p); }
+  __device__ __forceinline__ void get(float2 (&v)[CH / 2]) const { PixVec<T, CH>::f2(r, v); }
 };
 template <typename T, int CH> struct GBuf<T, CH, false> {  // arbitrary strides (roi_align_kernel.cu:253-256)
-  f32x2 v_[CH / 2];
+  float2 v_[CH / 2];
   __device__ __forceinline__ void load(const T* p, long long gs_c) {
 #pragma unroll
     for (int i = 0; i < CH / 2; ++i)
-      v_[i] = pack2((float)Io<T>::ld(p + lane_elem_channel<T, CH>(2 * i) * gs_c),
-                    (float)Io<T>::ld(p + lane_elem_channel<T, CH>(2 * i + 1) * gs_c));
+      v_[i] = make_float2((float)Io<T>::ld(p + lane_elem_channel<T, CH>(2 * i) * gs_c),
+                          (float)Io<T>::ld(p + lane_elem_channel<T, CH>(2 * i + 1) * gs_c));
   }
-  __device__ __forceinline__ void get(f32x2 (&v)[CH / 2]) const {
+  __device__ __forceinline__ void get(float2 (&v)[CH / 2]) const {
 #pragma unroll
     for (int i = 0; i < CH / 2; ++i) v[i] = v_[i];
   }
@@ -131,11 +131,12 @@ template <typename T, int CH, int SR, bool VEC>
 __device__ __forceinline__ void bwd_sweep(const BwdWarpTables& tb, int nrows, T* __restrict__ base,
                                           const T* __restrict__ g0p, const T* __restrict__ g1p, bool has1,
                                           long long gs_c, long long gs_w, int PW) {
-  using LV = LaneVec<T, CH>;
+  using PV = PixVec<T, CH>;
   constexpr int H2 = CH / 2;
-  f32x2 X0[H2], X1[H2], Y0[H2], Y1[H2], G0[H2], G1[H2];
+  const float2 zero2 = make_float2(0.f, 0.f);
+  float2 X0[H2], X1[H2], Y0[H2], Y1[H2], G0[H2], G1[H2];
 #pragma unroll
-  for (int i = 0; i < H2; ++i) { X0[i] = X1[i] = Y0[i] = Y1[i] = G0[i] = G1[i] = 0ull; }
+  for (int i = 0; i < H2; ++i) { X0[i] = X1[i] = Y0[i] = Y1[i] = G0[i] = G1[i] = zero2; }
   GBuf<T, CH, VEC> n0, n1;
   n0.load(g0p, gs_c);
   if (has1) n1.load(g1p, gs_c);
@@ -143,7 +144,7 @@ __device__ __forceinline__ void bwd_sweep(const BwdWarpTables& tb, int nrows, T*
   int j = 0;
   // samples j .. end-1 add into the window (lo, hi); the gradient of the next pooled
   // column is requested as soon as the current one has been taken over
-  auto samples = [&](int end, f32x2 (&lo0)[H2], f32x2 (&hi0)[H2], f32x2 (&lo1)[H2], f32x2 (&hi1)[H2]) {
+  auto samples = [&](int end, float2 (&lo0)[H2], float2 (&hi0)[H2], float2 (&lo1)[H2], float2 (&hi1)[H2]) {
 #pragma unroll 1
     for (; j < end; ++j) {
       if (SR == 1 || !(j & 1)) {
@@ -157,30 +158,30 @@ __device__ __forceinline__ void bwd_sweep(const BwdWarpTables& tb, int nrows, T*
       }
       const float4 s = tb.x.samp[j];
       if (__float_as_int(s.z)) {
-        const f32x2 hx = pack2(s.x, s.x), lx = pack2(s.y, s.y);
+        const float2 hx = make_float2(s.x, s.x), lx = make_float2(s.y, s.y);
 #pragma unroll
         for (int i = 0; i < H2; ++i) {
-          lo0[i] = fma2(hx, G0[i], lo0[i]);
-          hi0[i] = fma2(lx, G0[i], hi0[i]);
-          lo1[i] = fma2(hx, G1[i], lo1[i]);
-          hi1[i] = fma2(lx, G1[i], hi1[i]);
+          lo0[i] = __ffma2_rn(hx, G0[i], lo0[i]);
+          hi0[i] = __ffma2_rn(lx, G0[i], hi0[i]);
+          lo1[i] = __ffma2_rn(hx, G1[i], lo1[i]);
+          hi1[i] = __ffma2_rn(lx, G1[i], hi1[i]);
         }
       }
     }
   };
   // a column leaves the window: one vector red per distinct feature row
-  auto flush = [&](f32x2 (&a0)[H2], f32x2 (&a1)[H2], int co) {
+  auto flush = [&](float2 (&a0)[H2], float2 (&a1)[H2], int co) {
 #pragma unroll 1
     for (int r = 0; r < nrows; ++r) {
       const BYEnt e = tb.y[r];
-      const f32x2 w0 = pack2(e.w0, e.w0), w1 = pack2(e.w1, e.w1);
-      f32x2 v[H2];
+      const float2 w0 = make_float2(e.w0, e.w0), w1 = make_float2(e.w1, e.w1);
+      float2 v[H2];
 #pragma unroll
-      for (int i = 0; i < H2; ++i) v[i] = fma2(w0, a0[i], mul2(w1, a1[i]));
-      LV::red(base + (e.rowoff + co), v);
+      for (int i = 0; i < H2; ++i) v[i] = __ffma2_rn(w0, a0[i], __fmul2_rn(w1, a1[i]));
+      PV::red(base + (e.rowoff + co), v);
     }
 #pragma unroll
-    for (int i = 0; i < H2; ++i) { a0[i] = 0ull; a1[i] = 0ull; }
+    for (int i = 0; i < H2; ++i) { a0[i] = zero2; a1[i] = zero2; }
   };
 
   const int ncol = tb.x.ncol;
@@ -244,20 +245,17 @@ constexpr int kRowChunks = 4;
 template <typename T, int CH, int SR, int NR>
 __device__ __forceinline__ void rows_sweep(const XTab& xt, T* __restrict__ rowbase, const T* const (&gp)[NR],
                                            const float (&wy)[NR], long long gs_w, int PW) {
-  using LV = LaneVec<T, CH>;
+  using PV = PixVec<T, CH>;
   constexpr int H2 = CH / 2;
-  f32x2 wv[NR];
-  typename LV::raw n[NR];
+  const float2 zero2 = make_float2(0.f, 0.f);
+  typename PV::raw n[NR];
 #pragma unroll
-  for (int r = 0; r < NR; ++r) {
-    wv[r] = pack2(wy[r], wy[r]);
-    n[r] = LV::ld(gp[r]);
-  }
-  f32x2 X[H2], Y[H2], G[H2];
+  for (int r = 0; r < NR; ++r) PV::ld(n[r], gp[r]);
+  float2 X[H2], Y[H2], G[H2];
 #pragma unroll
-  for (int i = 0; i < H2; ++i) { X[i] = Y[i] = G[i] = 0ull; }
+  for (int i = 0; i < H2; ++i) { X[i] = Y[i] = G[i] = zero2; }
   int j = 0;
-  auto samples = [&](int end, f32x2 (&lo)[H2], f32x2 (&hi)[H2]) {
+  auto samples = [&](int end, float2 (&lo)[H2], float2 (&hi)[H2]) {
 #pragma unroll 1
     for (; j < end; ++j) {
       if (SR == 1 || !(j & 1)) {
@@ -265,28 +263,29 @@ __device__ __forceinline__ void rows_sweep(const XTab& xt, T* __restrict__ rowba
         const long long nxt = (long long)min(pwn, PW - 1) * gs_w;  // past the end: re-read the last column (L1)
 #pragma unroll
         for (int r = 0; r < NR; ++r) {
-          f32x2 t[H2];
-          LV::pairs(n[r], t);
+          float2 t[H2];
+          PV::f2(n[r], t);
+          const float2 w2 = make_float2(wy[r], wy[r]);
 #pragma unroll
-          for (int i = 0; i < H2; ++i) G[i] = (r == 0) ? mul2(wv[0], t[i]) : fma2(wv[r], t[i], G[i]);
-          n[r] = LV::ld(gp[r] + nxt);
+          for (int i = 0; i < H2; ++i) G[i] = (r == 0) ? __fmul2_rn(w2, t[i]) : __ffma2_rn(w2, t[i], G[i]);
+          PV::ld(n[r], gp[r] + nxt);
         }
       }
       const float4 s = xt.samp[j];
       if (__float_as_int(s.z)) {
-        const f32x2 hx = pack2(s.x, s.x), lx = pack2(s.y, s.y);
+        const float2 hx = make_float2(s.x, s.x), lx = make_float2(s.y, s.y);
 #pragma unroll
         for (int i = 0; i < H2; ++i) {
-          lo[i] = fma2(hx, G[i], lo[i]);
-          hi[i] = fma2(lx, G[i], hi[i]);
+          lo[i] = __ffma2_rn(hx, G[i], lo[i]);
+          hi[i] = __ffma2_rn(lx, G[i], hi[i]);
         }
       }
     }
   };
-  auto flush = [&](f32x2 (&a)[H2], int co) {
-    LV::red(rowbase + co, a);
+  auto flush = [&](float2 (&a)[H2], int co) {
+    PV::red(rowbase + co, a);
 #pragma unroll
-    for (int i = 0; i < H2; ++i) a[i] = 0ull;
+    for (int i = 0; i < H2; ++i) a[i] = zero2;
   };
   const int ncol = xt.ncol;
   samples(xt.ev_end[0], Y, X);

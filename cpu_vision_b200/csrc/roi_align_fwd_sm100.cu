@@ -85,70 +85,6 @@ __device__ __forceinline__ void build_y(const RoiGeom<float>& g, int H, int row_
   }
 }
 
-// ---- the lane's CH channels of one feature pixel ---------------------------------------------
-// as loaded (float4 / 32-bit words: ptxas uses the loaded registers in place, with LaneVec's 64-bit raw words it
-// copied them first) and as packed fp32 pairs for the sm_100 intrinsics __ffma2_rn / __fmul2_rn
-template <typename T, int CH> struct PixVec;
-template <int CH> struct PixVec<float, CH> {
-  struct raw { float4 v[CH / 4]; };
-  static __device__ __forceinline__ void ld(raw& r, const float* p) {
-#pragma unroll
-    for (int h = 0; h < CH / 4; ++h) r.v[h] = __ldg(reinterpret_cast<const float4*>(p + 128 * h));
-  }
-  static __device__ __forceinline__ void f2(const raw& r, float2 (&o)[CH / 2]) {
-#pragma unroll
-    for (int h = 0; h < CH / 4; ++h) {
-      o[2 * h] = make_float2(r.v[h].x, r.v[h].y);
-      o[2 * h + 1] = make_float2(r.v[h].z, r.v[h].w);
-    }
-  }
-  static __device__ __forceinline__ void st(float* p, const float2 (&v)[CH / 2]) {
-#pragma unroll
-    for (int h = 0; h < CH / 4; ++h)
-      __stcs(reinterpret_cast<float4*>(p + 128 * h), make_float4(v[2 * h].x, v[2 * h].y, v[2 * h + 1].x, v[2 * h + 1].y));
-  }
-};
-template <typename T> struct Cvt2;
-template <> struct Cvt2<__nv_bfloat16> {
-  static __device__ __forceinline__ float2 widen(unsigned u) {
-    return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
-  }
-  static __device__ __forceinline__ unsigned narrow(float2 v) {
-    const __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
-    return *reinterpret_cast<const unsigned*>(&h);
-  }
-};
-template <> struct Cvt2<__half> {
-  static __device__ __forceinline__ float2 widen(unsigned u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); }
-  static __device__ __forceinline__ unsigned narrow(float2 v) {
-    const __half2 h = __floats2half2_rn(v.x, v.y);
-    return *reinterpret_cast<const unsigned*>(&h);
-  }
-};
-template <typename T, int CH> struct PixVec {   // 16-bit elements: CH * 2 contiguous bytes per lane
-  struct raw { unsigned u[CH / 2]; };
-  static __device__ __forceinline__ void ld(raw& r, const T* p) {
-    if (CH == 8) {
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
-      r.u[0] = v.x; r.u[1] = v.y; r.u[CH / 2 - 2] = v.z; r.u[CH / 2 - 1] = v.w;
-    } else {
-      const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
-      r.u[0] = v.x; r.u[1] = v.y;
-    }
-  }
-  static __device__ __forceinline__ void f2(const raw& r, float2 (&o)[CH / 2]) {
-#pragma unroll
-    for (int i = 0; i < CH / 2; ++i) o[i] = Cvt2<T>::widen(r.u[i]);
-  }
-  static __device__ __forceinline__ void st(T* p, const float2 (&v)[CH / 2]) {
-    if (CH == 8)
-      __stcs(reinterpret_cast<uint4*>(p), make_uint4(Cvt2<T>::narrow(v[0]), Cvt2<T>::narrow(v[1]),
-                                                      Cvt2<T>::narrow(v[CH / 2 - 2]), Cvt2<T>::narrow(v[CH / 2 - 1])));
-    else
-      __stcs(reinterpret_cast<uint2*>(p), make_uint2(Cvt2<T>::narrow(v[0]), Cvt2<T>::narrow(v[1])));
-  }
-};
-
 // ---- one pooled row -----------------------------------------------------------------------
 template <typename T, int CH, int SR, int NR>
 __device__ __forceinline__ void sweep_row(const FwdTables& tb, const T* __restrict__ base, T* __restrict__ o,

@@ -155,6 +155,101 @@ template <> struct LaneVec<__half, 8> : LaneVec16x8<__half> {};
 template <> struct LaneVec<__nv_bfloat16, 4> : LaneVec16x4<__nv_bfloat16> {};
 template <> struct LaneVec<__nv_bfloat16, 8> : LaneVec16x8<__nv_bfloat16> {};
 
+// ---- the lane's CH channels of one pixel, float2 flavour --------------------------------------
+// Same channel assignment as LaneVec, but loaded as float4 / 32-bit words and handed out as float2 for the sm_100
+// packed-fp32 intrinsics (__ffma2_rn, __fmul2_rn, __fadd2_rn).  With these ptxas updates accumulators in place
+// and uses loaded registers directly; with LaneVec's opaque 64-bit asm operands it copied every packed sum back
+// (12 MOVs per sample in the strip sweep, half of the forward's SASS): measured in round 2.
+template <typename T> struct Cvt2;
+template <> struct Cvt2<__nv_bfloat16> {
+  static __device__ __forceinline__ float2 widen(unsigned u) {
+    return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
+  }
+  static __device__ __forceinline__ unsigned narrow(float2 v) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+    return *reinterpret_cast<const unsigned*>(&h);
+  }
+};
+template <> struct Cvt2<__half> {
+  static __device__ __forceinline__ float2 widen(unsigned u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); }
+  static __device__ __forceinline__ unsigned narrow(float2 v) {
+    const __half2 h = __floats2half2_rn(v.x, v.y);
+    return *reinterpret_cast<const unsigned*>(&h);
+  }
+};
+
+template <typename T, int CH> struct PixVec;
+template <int CH> struct PixVec<float, CH> {
+  struct raw { float4 v[CH / 4]; };
+  static __device__ __forceinline__ void ld(raw& r, const float* p) {
+#pragma unroll
+    for (int h = 0; h < CH / 4; ++h) r.v[h] = __ldg(reinterpret_cast<const float4*>(p + 128 * h));
+  }
+  static __device__ __forceinline__ void ld_stream(raw& r, const float* p) {
+#pragma unroll
+    for (int h = 0; h < CH / 4; ++h) r.v[h] = __ldcs(reinterpret_cast<const float4*>(p + 128 * h));
+  }
+  static __device__ __forceinline__ void f2(const raw& r, float2 (&o)[CH / 2]) {
+#pragma unroll
+    for (int h = 0; h < CH / 4; ++h) {
+      o[2 * h] = make_float2(r.v[h].x, r.v[h].y);
+      o[2 * h + 1] = make_float2(r.v[h].z, r.v[h].w);
+    }
+  }
+  static __device__ __forceinline__ void st(float* p, const float2 (&v)[CH / 2]) {
+#pragma unroll
+    for (int h = 0; h < CH / 4; ++h)
+      __stcs(reinterpret_cast<float4*>(p + 128 * h), make_float4(v[2 * h].x, v[2 * h].y, v[2 * h + 1].x, v[2 * h + 1].y));
+  }
+  // one vector reduction per 16 bytes: red.global.add.v4.f32 (sm_90+)
+  static __device__ __forceinline__ void red(float* p, const float2 (&v)[CH / 2]) {
+#pragma unroll
+    for (int h = 0; h < CH / 4; ++h)
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p + 128 * h), "f"(v[2 * h].x), "f"(v[2 * h].y),
+                   "f"(v[2 * h + 1].x), "f"(v[2 * h + 1].y) : "memory");
+  }
+};
+template <typename T, int CH> struct PixVec {   // 16-bit elements: CH * 2 contiguous bytes per lane
+  struct raw { unsigned u[CH / 2]; };
+  static __device__ __forceinline__ void ld(raw& r, const T* p) {
+    if (CH == 8) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+      r.u[0] = v.x; r.u[1] = v.y; r.u[CH / 2 - 2] = v.z; r.u[CH / 2 - 1] = v.w;
+    } else {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+      r.u[0] = v.x; r.u[1] = v.y;
+    }
+  }
+  static __device__ __forceinline__ void ld_stream(raw& r, const T* p) {
+    if (CH == 8) {
+      const uint4 v = __ldcs(reinterpret_cast<const uint4*>(p));
+      r.u[0] = v.x; r.u[1] = v.y; r.u[CH / 2 - 2] = v.z; r.u[CH / 2 - 1] = v.w;
+    } else {
+      const uint2 v = __ldcs(reinterpret_cast<const uint2*>(p));
+      r.u[0] = v.x; r.u[1] = v.y;
+    }
+  }
+  static __device__ __forceinline__ void f2(const raw& r, float2 (&o)[CH / 2]) {
+#pragma unroll
+    for (int i = 0; i < CH / 2; ++i) o[i] = Cvt2<T>::widen(r.u[i]);
+  }
+  static __device__ __forceinline__ void st(T* p, const float2 (&v)[CH / 2]) {
+    if (CH == 8)
+      __stcs(reinterpret_cast<uint4*>(p), make_uint4(Cvt2<T>::narrow(v[0]), Cvt2<T>::narrow(v[1]),
+                                                      Cvt2<T>::narrow(v[CH / 2 - 2]), Cvt2<T>::narrow(v[CH / 2 - 1])));
+    else
+      __stcs(reinterpret_cast<uint2*>(p), make_uint2(Cvt2<T>::narrow(v[0]), Cvt2<T>::narrow(v[1])));
+  }
+  // packed 16-bit reductions: red.global.add.noftz.v4 / v2 .bf16x2 / .f16x2
+  static __device__ __forceinline__ void red(T* p, const float2 (&v)[CH / 2]) {
+    if (CH == 8)
+      Cvt16<T>::red4(p, Cvt2<T>::narrow(v[0]), Cvt2<T>::narrow(v[1]), Cvt2<T>::narrow(v[CH / 2 - 2]),
+                     Cvt2<T>::narrow(v[CH / 2 - 1]));
+    else
+      Cvt16<T>::red2(p, Cvt2<T>::narrow(v[0]), Cvt2<T>::narrow(v[1]));
+  }
+};
+
 // first channel a lane owns inside its tile (the second half of LaneVec<float, 8>
 // sits 128 channels further)
 template <typename T, int CH>
