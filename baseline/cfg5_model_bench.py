@@ -70,6 +70,11 @@ with torch.no_grad():
     pool = lambda: heads.box_roi_pool(features, props, shapes)
     res["box_roi_pool_ms"] = timed(pool)
     res["rois"] = sum(p.shape[0] for p in props)
+    # the same call when the backbone hands over channels_last features (model.to(memory_format=channels_last)):
+    # no re-layout passes around the kernels
+    from collections import OrderedDict
+    feats_cl = OrderedDict((k, v.contiguous(memory_format=torch.channels_last)) for k, v in features.items())
+    res["box_roi_pool_channels_last_features_ms"] = timed(lambda: heads.box_roi_pool(feats_cl, props, shapes))
     box_features = pool()
     head = lambda: heads.box_predictor(heads.box_head(box_features))
     res["box_head_predictor_ms"] = timed(head)
