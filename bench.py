@@ -322,8 +322,8 @@ def run_b200(args, rank, world, local):
     out_bytes = K * C * ph * ph * es
     algo = {"fwd": feat_bytes + out_bytes + K * 20, "bwd": out_bytes + feat_bytes + K * 20}
     peak, peak_src = measured_peak()
-    # DRAM bytes of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json,
-    # written by hand from profiles/*.ncu.txt after each capture); null when no capture matches
+    # DRAM bytes of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json, written by
+    # tools/ncu_summary.py --traffic from the same .ncu-rep as the text summary); null when no capture matches
     traffic = {}
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:

@@ -102,7 +102,39 @@ def source(rep, top=16):
             print(f"    {s:7d} {e:10d}  {src}")
 
 
+def traffic(rep, workload, out_txt):
+    """Writes the DRAM bytes per launch of the forward / backward kernels of `rep` into profiles/traffic.json under
+    `workload` (what bench.py reports as roofline.traffic): dram__bytes_read.sum + dram__bytes_write.sum, units
+    taken from the report."""
+    import json
+    import os
+
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    rows = list(csv.reader(ncu(rep, "raw").splitlines()))
+    hdr, units = rows[0], rows[1]
+    ir, iw, iname = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
+    res = {}
+    for r in rows[2:]:
+        name = r[iname]
+        key = "fwd" if "fwd" in name else ("bwd" if "bwd" in name else None)
+        if key and key not in res:
+            res[key] = int(float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]])
+    res["source"] = f"{out_txt} (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch; written by tools/ncu_summary.py --traffic)"
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "traffic.json")
+    try:
+        allt = json.load(open(path))
+    except Exception:
+        allt = {}
+    allt[workload] = res
+    json.dump(allt, open(path, "w"), indent=1)
+    print(f"# traffic.json[{workload}] = {res}", file=sys.stderr)
+
+
 if __name__ == "__main__":
+    # python tools/ncu_summary.py x.ncu-rep [--traffic WORKLOAD profiles/x.ncu.txt] > profiles/x.ncu.txt
+    if "--traffic" in sys.argv:
+        i = sys.argv.index("--traffic")
+        traffic(sys.argv[1], sys.argv[i + 1], sys.argv[i + 2])
     rep = sys.argv[1]
     print(f"# ncu summary of {rep} (ncu --set full --clock-control none --import-source on; cold-cache, serialised)")
     raw(rep)
