@@ -29,6 +29,7 @@ SYMBOLS = [
     "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented", "b200det_clip_filter_boxes", "b200det_relayout",
     "b200det_roi_pool_forward", "b200det_roi_pool_backward", "b200det_ps_roi_pool_forward",
     "b200det_ps_roi_pool_backward", "b200det_ps_roi_align_forward", "b200det_ps_roi_align_backward",
+    "b200det_rpn_select", "b200det_roi_heads_decode",
 ]
 
 _declared = False
@@ -66,6 +67,8 @@ def lib():
         l.b200det_nms_segmented.argtypes = [_P, _P, _P, _P, _I, _L, _P, _L, _D, _I, _L, _P, _P, _P, _S, _P]
         l.b200det_clip_filter_boxes.argtypes = [_P, _P, _I, _L, _P, _L, _P, _D, _D, _I, _P, _P, _P]
         l.b200det_relayout.argtypes = [_P, _P, _I, _L, _L, _L, _P]
+        l.b200det_rpn_select.argtypes = [_P, _P, _P, _L, _L, _L, _P, _P, _I, _D, _D, _P, _P, _P, _P, _P]
+        l.b200det_roi_heads_decode.argtypes = [_P, _P, _P, _P, _P, _L, _L, _P, _D, _D, _D, _P, _P, _P, _P]
         l.b200det_roi_pool_forward.argtypes = [_P, _I, _P, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _P]
         l.b200det_roi_pool_backward.argtypes = [_P, _P, _P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _P]
         l.b200det_ps_roi_pool_forward.argtypes = [_P, _I, _P, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _P]
@@ -303,6 +306,53 @@ def clip_filter_boxes(boxes, scores, seg_offsets: Sequence[int], image_shapes, m
                                                int(bool(strict)), out.data_ptr(), valid.data_ptr(), _stream(boxes)),
                "b200det_clip_filter_boxes")
     return out, valid[:n]
+
+
+def rpn_select(proposals, objectness, top_idx, image_shapes, num_anchors_per_level, min_size, score_thresh):
+    """b200det_rpn_select: [B, A, 4] fp32 proposals, [B, A] logits, int64 [B, P] top-k indices ->
+    (boxes [B*P, 4], scores [B*P], levels int64 [B*P], valid uint8 [B*P])."""
+    proposals, objectness, top_idx = proposals.contiguous(), objectness.contiguous(), top_idx.contiguous()
+    B, A = objectness.shape
+    P = top_idx.shape[1]
+    dev = proposals.device
+    sizes = torch.tensor([[float(h), float(w)] for h, w in image_shapes], dtype=torch.float32, device=dev)
+    ends, acc = [], 0
+    for n in num_anchors_per_level:
+        acc += int(n)
+        ends.append(acc)
+    le = (C.c_int32 * len(ends))(*ends)
+    boxes = torch.empty(B * P, 4, dtype=torch.float32, device=dev)
+    scores = torch.empty(B * P, dtype=torch.float32, device=dev)
+    levels = torch.empty(B * P, dtype=torch.int64, device=dev)
+    valid = torch.empty(max(B * P, 1), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _check(lib().b200det_rpn_select(proposals.data_ptr(), objectness.data_ptr(), top_idx.data_ptr(), B, A, P,
+                                        sizes.data_ptr(), le, len(ends), float(min_size), float(score_thresh),
+                                        boxes.data_ptr(), scores.data_ptr(), levels.data_ptr(), valid.data_ptr(),
+                                        _stream(proposals)), "b200det_rpn_select")
+    return boxes, scores, levels, valid[:B * P]
+
+
+def roi_heads_decode(class_logits, box_regression, proposals, image_of, image_shapes, weights, xform_clip,
+                     score_thresh, min_size):
+    """b200det_roi_heads_decode: fp32 [R, NC] logits, [R, NC*4] regression, [R, 4] proposals, int32 [R] image index
+    -> (boxes [R*(NC-1), 4], scores [R*(NC-1)], valid uint8 [R*(NC-1)])."""
+    class_logits, box_regression, proposals = class_logits.contiguous(), box_regression.contiguous(), proposals.contiguous()
+    R, NC = class_logits.shape
+    dev = class_logits.device
+    sizes = torch.tensor([[float(h), float(w)] for h, w in image_shapes], dtype=torch.float32, device=dev)
+    n = R * max(NC - 1, 0)
+    boxes = torch.empty(n, 4, dtype=torch.float32, device=dev)
+    scores = torch.empty(n, dtype=torch.float32, device=dev)
+    valid = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
+    w = (C.c_double * 4)(*[float(x) for x in weights])
+    with torch.cuda.device(dev):
+        _check(lib().b200det_roi_heads_decode(class_logits.data_ptr(), box_regression.data_ptr(), proposals.data_ptr(),
+                                              image_of.contiguous().data_ptr(), sizes.data_ptr(), R, NC, w,
+                                              float(xform_clip), float(score_thresh), float(min_size),
+                                              boxes.data_ptr(), scores.data_ptr(), valid.data_ptr(),
+                                              _stream(class_logits)), "b200det_roi_heads_decode")
+    return boxes, scores, valid[:n]
 
 
 def relayout(t, to_channels_last: bool):

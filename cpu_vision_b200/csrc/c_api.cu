@@ -313,6 +313,37 @@ int b200det_clip_filter_boxes(const void* boxes, const void* scores, int dtype, 
                            strict, boxes_out, valid, (cudaStream_t)stream);
 }
 
+int b200det_rpn_select(const void* proposals, const void* objectness, const int64_t* top_idx, int64_t B, int64_t A,
+                       int64_t P, const float* image_sizes_dev, const int32_t* level_ends, int num_levels,
+                       double min_size, double score_thresh, void* boxes_out, void* scores_out, int64_t* levels_out,
+                       uint8_t* valid, void* stream) {
+  if (B < 0 || A < 0 || P < 0) return fail(B200DET_EINVAL, "rpn_select: negative size");
+  if (B * P == 0) return 0;
+  if (B > 0x7fffffffLL || P > 0x7fffffffLL || num_levels < 1 || num_levels > 8)
+    return fail(B200DET_EINVAL, "rpn_select: B, P < 2^31 and 1..8 levels expected");
+  if (!proposals || !objectness || !top_idx || !image_sizes_dev || !level_ends || !boxes_out || !scores_out ||
+      !levels_out || !valid)
+    return fail(B200DET_EINVAL, "rpn_select: null pointer");
+  return rpn_select((const float*)proposals, (const float*)objectness, top_idx, (int)B, A, (int)P, image_sizes_dev,
+                    level_ends, num_levels, min_size, score_thresh, (float*)boxes_out, (float*)scores_out, levels_out,
+                    valid, (cudaStream_t)stream);
+}
+
+int b200det_roi_heads_decode(const void* class_logits, const void* box_regression, const void* proposals,
+                             const int32_t* image_of, const float* image_sizes_dev, int64_t R, int64_t NC,
+                             const double* weights, double bbox_xform_clip, double score_thresh, double min_size,
+                             void* boxes_out, void* scores_out, uint8_t* valid, void* stream) {
+  if (R < 0 || NC < 0) return fail(B200DET_EINVAL, "roi_heads_decode: negative size");
+  if (R == 0 || NC < 2) return 0;
+  if (R > 0x7fffffffLL / 64 || NC > 65536) return fail(B200DET_EINVAL, "roi_heads_decode: R or NC too large");
+  if (!class_logits || !box_regression || !proposals || !image_of || !image_sizes_dev || !weights || !boxes_out ||
+      !scores_out || !valid)
+    return fail(B200DET_EINVAL, "roi_heads_decode: null pointer");
+  return roi_heads_decode((const float*)class_logits, (const float*)box_regression, (const float*)proposals, image_of,
+                          image_sizes_dev, (int)R, (int)NC, weights, bbox_xform_clip, score_thresh, min_size,
+                          (float*)boxes_out, (float*)scores_out, valid, (cudaStream_t)stream);
+}
+
 int b200det_relayout(const void* src, void* dst, int dtype, int64_t batch, int64_t rows, int64_t cols,
                      void* stream) {
   if (batch < 0 || rows < 0 || cols < 0) return fail(B200DET_EINVAL, "relayout: negative size");

@@ -68,6 +68,15 @@ int clip_filter_boxes(const void* boxes, const void* scores, int dtype, long lon
                       const float* sizes, double min_size, double score_thresh, int strict, void* out,
                       uint8_t* valid, cudaStream_t st);
 
+// box_ops_sm100.cu: the RPN side between top-k and NMS in one pass (gather, sigmoid, level, clip, filters), fp32
+int rpn_select(const float* proposals, const float* objectness, const int64_t* top_idx, int B, long long A, int P,
+               const float* sizes, const int* level_ends, int num_levels, double min_size, double score_thresh,
+               float* boxes, float* scores, int64_t* levels, uint8_t* valid, cudaStream_t st);
+// box_ops_sm100.cu: the RoIHeads side before NMS in one pass (softmax, BoxCoder.decode, clip, filters), fp32
+int roi_heads_decode(const float* logits, const float* reg, const float* props, const int32_t* image_of,
+                     const float* sizes, int R, int NC, const double* weights, double xform_clip, double score_thresh,
+                     double min_size, float* boxes, float* scores, uint8_t* valid, cudaStream_t st);
+
 // relayout_sm100.cu: dst[b][c][r] = src[b][r][c] (NCHW -> NHWC: R = C, S = H*W; back: R = H*W, S = C)
 int relayout(const void* src, void* dst, int dtype, long long B, long long R, long long S, cudaStream_t st);
 

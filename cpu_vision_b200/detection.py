@@ -62,22 +62,24 @@ def filter_proposals(proposals: Tensor, objectness: Tensor, image_shapes: List[T
     num_images = proposals.shape[0]
     device = proposals.device
     objectness = objectness.detach().reshape(num_images, -1)
-    levels = torch.cat([torch.full((n,), idx, dtype=torch.int64, device=device)
-                        for idx, n in enumerate(num_anchors_per_level)], 0)
-    levels = levels.reshape(1, -1).expand_as(objectness)
     top_n_idx = _get_top_n_idx(objectness, num_anchors_per_level, pre_nms_top_n)
-    batch_idx = torch.arange(num_images, device=device)[:, None]
-    objectness = objectness[batch_idx, top_n_idx]
-    levels = levels[batch_idx, top_n_idx]
-    proposals = proposals[batch_idx, top_n_idx]
-    scores = torch.sigmoid(objectness)
-
-    per = proposals.shape[1]
+    per = top_n_idx.shape[1]
     off = [i * per for i in range(num_images + 1)]
-    boxes, valid = capi.clip_filter_boxes(proposals.reshape(-1, 4), scores.reshape(-1), off, image_shapes, min_size,
-                                          score_thresh, strict=False)
-    flat_scores = scores.reshape(-1).contiguous()
-    keep, counts = capi.nms_segmented(boxes, flat_scores, levels.reshape(-1), off, nms_thresh, valid=valid,
+    if proposals.dtype == torch.float32 and objectness.dtype == torch.float32 and len(num_anchors_per_level) <= 8:
+        # ONE kernel between top-k and NMS: gather of the selected anchors, sigmoid, pyramid level, clip, filters
+        boxes, flat_scores, flat_levels, valid = capi.rpn_select(proposals, objectness, top_n_idx, image_shapes,
+                                                                 num_anchors_per_level, min_size, score_thresh)
+    else:  # other dtypes: the same steps as library ops + the clip / filter kernel
+        levels = torch.cat([torch.full((n,), idx, dtype=torch.int64, device=device)
+                            for idx, n in enumerate(num_anchors_per_level)], 0)
+        levels = levels.reshape(1, -1).expand_as(objectness)
+        batch_idx = torch.arange(num_images, device=device)[:, None]
+        scores = torch.sigmoid(objectness[batch_idx, top_n_idx])
+        flat_levels = levels[batch_idx, top_n_idx].reshape(-1)
+        boxes, valid = capi.clip_filter_boxes(proposals[batch_idx, top_n_idx].reshape(-1, 4), scores.reshape(-1), off,
+                                              image_shapes, min_size, score_thresh, strict=False)
+        flat_scores = scores.reshape(-1).contiguous()
+    keep, counts = capi.nms_segmented(boxes, flat_scores, flat_levels, off, nms_thresh, valid=valid,
                                       top_n=post_nms_top_n, sync=False)
     final_boxes, final_scores = _gather_kept(keep, counts, off, boxes, flat_scores)
     return final_boxes, final_scores
@@ -117,17 +119,24 @@ def postprocess_detections(class_logits: Tensor, box_regression: Tensor, proposa
     boxes_per_image = [b.shape[0] for b in proposals]
     R = sum(boxes_per_image)
     concat = torch.cat(proposals, 0)
-    pred_boxes = decode_boxes(box_regression.reshape(R, -1) if R > 0 else box_regression, concat, bbox_reg_weights)
-    pred_boxes = pred_boxes.reshape(R, -1, 4)
-    pred_scores = F.softmax(class_logits, -1)
-    # drop the background column, one instance per (proposal, class): roi_heads.py:697-705
-    boxes = pred_boxes[:, 1:].reshape(-1, 4)
-    scores = pred_scores[:, 1:].reshape(-1).contiguous()
-    labels = torch.arange(1, num_classes, device=device).repeat(R)
     off = [0]
     for n in boxes_per_image:
         off.append(off[-1] + n * (num_classes - 1))
-    boxes, valid = capi.clip_filter_boxes(boxes, scores, off, image_shapes, 1e-2, score_thresh, strict=True)
+    if class_logits.dtype == torch.float32 and box_regression.dtype == torch.float32 and concat.dtype == torch.float32:
+        # ONE kernel before NMS: softmax, BoxCoder.decode, clip, score and small-box filters (a warp per proposal)
+        image_of = torch.repeat_interleave(torch.arange(len(boxes_per_image), dtype=torch.int32, device=device),
+                                           torch.tensor(boxes_per_image, device=device))
+        boxes, scores, valid = capi.roi_heads_decode(class_logits, box_regression.reshape(R, -1), concat, image_of,
+                                                     image_shapes, bbox_reg_weights, math.log(1000.0 / 16), score_thresh,
+                                                     1e-2)
+    else:
+        pred_boxes = decode_boxes(box_regression.reshape(R, -1) if R > 0 else box_regression, concat, bbox_reg_weights)
+        pred_boxes = pred_boxes.reshape(R, -1, 4)
+        pred_scores = F.softmax(class_logits, -1)
+        # drop the background column, one instance per (proposal, class): roi_heads.py:697-705
+        boxes = pred_boxes[:, 1:].reshape(-1, 4)
+        scores = pred_scores[:, 1:].reshape(-1).contiguous()
+        boxes, valid = capi.clip_filter_boxes(boxes, scores, off, image_shapes, 1e-2, score_thresh, strict=True)
     # The score filter drops most of the (proposal, class) instances (1000 proposals x 90 classes per image,
     # a few hundred above 0.05) and NMS is quadratic in the set size, so unlike the RPN side -- where nearly
     # every candidate survives and the shapes stay static -- the survivors are compacted first: ONE read-back of
@@ -136,7 +145,8 @@ def postprocess_detections(class_logits: Tensor, box_regression: Tensor, proposa
     ends = csum[torch.tensor(off, device=device)].tolist()
     off2 = [e - ends[0] for e in ends]
     vidx = valid.nonzero().squeeze(1)
-    boxes, scores, labels = boxes[vidx], scores[vidx], labels[vidx]
+    # instance r * (num_classes - 1) + (c - 1) has label c (the reference's arange(num_classes)[1:] per proposal)
+    boxes, scores, labels = boxes[vidx], scores[vidx], vidx % (num_classes - 1) + 1
     keep, counts = capi.nms_segmented(boxes, scores, labels, off2, nms_thresh, top_n=detections_per_img, sync=False)
     all_boxes, all_scores, all_labels = _gather_kept(keep, counts, off2, boxes, scores, labels)
     return all_boxes, all_scores, all_labels

@@ -222,6 +222,32 @@ int b200det_clip_filter_boxes(
     double min_size, double score_thresh, int strict, void* boxes_out,
     uint8_t* valid, void* stream);
 
+/* The RPN side between the per-level top-k and NMS in ONE pass (torchvision/models/detection/rpn.py:258-285,
+ * all images at once): candidate (b, j) takes anchor a = top_idx[b][j]; boxes_out = clip(proposals[b][a]),
+ * scores_out = sigmoid(objectness[b][a]) (1 / (1 + exp(-x)) in fp32, as torch computes it on CUDA), levels_out =
+ * the pyramid level of anchor a, valid = small-box (min_size) and score (>=) filters.  fp32 tensors.
+ *   proposals [B, A, 4], objectness [B, A], top_idx int64 [B, P] (indices into A)
+ *   image_sizes_dev: DEVICE float [B, 2] (height, width);  level_ends: HOST int[num_levels <= 8], cumulative
+ *   anchors per level;  outputs: boxes_out [B*P, 4], scores_out [B*P], levels_out int64 [B*P], valid uint8 [B*P] */
+int b200det_rpn_select(
+    const void* proposals, const void* objectness, const int64_t* top_idx,
+    int64_t B, int64_t A, int64_t P, const float* image_sizes_dev,
+    const int32_t* level_ends, int num_levels, double min_size, double score_thresh,
+    void* boxes_out, void* scores_out, int64_t* levels_out, uint8_t* valid, void* stream);
+
+/* The RoIHeads side before NMS in ONE pass (torchvision/models/detection/roi_heads.py:682-716 with
+ * BoxCoder.decode, models/detection/_utils.py:162-224): softmax over the NC class logits, the box of every class
+ * c >= 1 decoded from box_regression in the reference's operation order, clipped to the proposal's image, and
+ * the validity byte of the score (>) and small-box (min_size) filters.  Instance r * (NC - 1) + (c - 1).  fp32.
+ *   class_logits [R, NC], box_regression [R, NC * 4], proposals [R, 4], image_of DEVICE int32 [R] (image of a
+ *   proposal), image_sizes_dev DEVICE float [S, 2], weights HOST double[4] (wx, wy, ww, wh), bbox_xform_clip
+ *   outputs: boxes_out [R * (NC - 1), 4], scores_out [R * (NC - 1)], valid uint8 [R * (NC - 1)] */
+int b200det_roi_heads_decode(
+    const void* class_logits, const void* box_regression, const void* proposals,
+    const int32_t* image_of, const float* image_sizes_dev, int64_t R, int64_t NC,
+    const double* weights, double bbox_xform_clip, double score_thresh, double min_size,
+    void* boxes_out, void* scores_out, uint8_t* valid, void* stream);
+
 /* Batched transposition dst[b][c][r] = src[b][r][c] of `batch` dense
  * [rows, cols] matrices: the NCHW <-> NHWC re-layout the dispatcher shim puts
  * around the channels_last kernels for callers that hold NCHW-contiguous
