@@ -1,10 +1,11 @@
 // nms_sm100.cu -- greedy NMS and class-aware NMS, entirely on the device.
 //
 // Pipeline (all on the caller's stream, no host round trip):
-//   1-3. up to 8192 boxes: nms_front_small_kernel -- ONE CTA builds the fp32 sort keys, block-radix-sorts
-//        them (stable: ties keep ascending original index like scores.sort(stable=True, descending=True),
-//        cuda/nms_kernel.cu:112-113), reduces boxes.max() for the coordinate trick (boxes.py:91-93) and
-//        gathers the boxes into score order.  Larger sets / fp64 scores: nms_prepare_kernel,
+//   1-3. up to 8192 boxes: nms_front_rank_kernel -- every CTA stages all fp32 sort keys in shared memory and ranks
+//        64 of them by counting (stable: ties keep ascending original index like scores.sort(stable=True,
+//        descending=True), cuda/nms_kernel.cu:112-113), reduces boxes.max() for the coordinate trick
+//        (boxes.py:91-93) and gathers its boxes into score order (B200DET_NMS_FRONT=block: the one-CTA block
+//        radix sort nms_front_small_kernel).  Larger sets / fp64 scores: nms_prepare_kernel,
 //        cub::DeviceRadixSort::SortPairsDescending, nms_max_coord_kernel, nms_gather_kernel.
 //   4. nms_mask_kernel      upper-triangular 64x64 IoU>thr bit tiles
 //                           (replaces nms_kernel_impl, cuda/nms_kernel.cu:31-78)
@@ -16,6 +17,8 @@
 // IoU follows devIoU (cuda/nms_kernel.cu:16-29) with every operation an
 // explicit round-to-nearest intrinsic so no FMA contraction can change a
 // comparison: inter / ((Sa + Sb) - inter) > (float)threshold.
+#include <stdlib.h>
+
 #include <type_traits>
 #include <cub/block/block_radix_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
@@ -250,6 +253,91 @@ __global__ void __launch_bounds__(kSortThreads) nms_front_small_kernel(
     sorted[p] = b;
     if (sorted_cls) sorted_cls[p] = (int32_t)idxs[src];
   }
+}
+
+// ---- 1-3 fused, over all SMs: rank sort ------------------------------------------
+// The block radix sort above runs on ONE SM (8 passes of ranking + exchange over 8192 slots, ~35 us for 5000
+// boxes) while 147 SMs wait.  A detection-sized set fits every SM's shared memory, so each CTA stages ALL n keys
+// (n * 4 bytes), and ranks kRankKeys of them by counting: rank(i) = #{j : key_j > key_i} + #{j < i : key_j == key_i},
+// which is exactly the position a stable descending sort gives box i.  kRankSplit threads share the count of one
+// key (16-byte shared loads, the same address for the threads of a warp that hold the same part: broadcasts).
+// n^2 / 4 compares spread over n / 64 CTAs: 5000 boxes -> 79 CTAs x 1250 compares per thread.
+// Keys are compared as cub compares floats (radix order: sign-flipped bit patterns, -0 ranks with +0), so ties,
+// NaN scores and signed zeros land where the block sort and the device-wide sort put them.
+constexpr int kRankKeys = 64, kRankSplit = 4, kRankThreads = kRankKeys * kRankSplit;
+
+__device__ __forceinline__ unsigned radix_order_key(float f) {
+  unsigned b = __float_as_uint(f);
+  if (b == 0x80000000u) b = 0u;
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kRankThreads) nms_front_rank_kernel(
+    const T* __restrict__ boxes, const T* __restrict__ scores, const int64_t* __restrict__ idxs, int n, int mode,
+    Box4f* __restrict__ sorted, int32_t* __restrict__ sorted_cls, int32_t* __restrict__ order) {
+  extern __shared__ __align__(16) unsigned s_key[];  // n rounded up to 4, padding = 0 (below every real key's tie rule)
+  __shared__ float red[kRankThreads / 32];
+  __shared__ float s_max;
+  pdl_launch_dependents();
+  const int tid = threadIdx.x;
+  const int n4 = (n + 3) >> 2;
+  for (int i = tid; i < n4 * 4; i += kRankThreads) s_key[i] = i < n ? radix_order_key((float)Io<T>::ld(scores + i)) : 0u;
+  if (mode == 1) {  // boxes.max() as nms_max_coord_kernel computes it (NaN propagates); every CTA needs it
+    float m = -INFINITY;
+    bool nan = false;
+    for (int i = tid; i < 4 * n; i += kRankThreads) {
+      const float x = Io<T>::ld(boxes + i);
+      nan |= (x != x);
+      m = x > m ? x : m;
+    }
+    if (nan) m = NAN;
+    for (int o = 16; o > 0; o >>= 1) {
+      const float other = __shfl_xor_sync(0xffffffffu, m, o);
+      m = (other != other || m != m) ? NAN : (other > m ? other : m);
+    }
+    if ((tid & 31) == 0) red[tid >> 5] = m;
+  }
+  __syncthreads();
+  if (mode == 1 && tid < 32) {
+    float m = tid < kRankThreads / 32 ? red[tid] : -INFINITY;
+    for (int o = 16; o > 0; o >>= 1) {
+      const float other = __shfl_xor_sync(0xffffffffu, m, o);
+      m = (other != other || m != m) ? NAN : (other > m ? other : m);
+    }
+    if (tid == 0) s_max = m;
+  }
+  const int part = tid % kRankSplit;
+  const int i = blockIdx.x * kRankKeys + tid / kRankSplit;
+  int rank = 0;
+  if (i < n) {
+    const unsigned ki = s_key[i];
+    const uint4* k4 = reinterpret_cast<const uint4*>(s_key);
+    for (int q = part; q < n4; q += kRankSplit) {
+      const uint4 k = k4[q];
+      const int j = q * 4;
+      rank += (k.x > ki) | ((k.x == ki) & (j + 0 < i));
+      rank += (k.y > ki) | ((k.y == ki) & (j + 1 < i));
+      rank += (k.z > ki) | ((k.z == ki) & (j + 2 < i));
+      rank += (k.w > ki) | ((k.w == ki) & (j + 3 < i));
+    }
+  }
+  rank += __shfl_xor_sync(0xffffffffu, rank, 1);
+  rank += __shfl_xor_sync(0xffffffffu, rank, 2);
+  __syncthreads();  // s_max
+  if (i >= n || part != 0) return;
+  order[rank] = i;
+  float x1 = Io<T>::ld(boxes + (size_t)i * 4 + 0), y1 = Io<T>::ld(boxes + (size_t)i * 4 + 1);
+  float x2 = Io<T>::ld(boxes + (size_t)i * 4 + 2), y2 = Io<T>::ld(boxes + (size_t)i * 4 + 3);
+  if (mode == 1) {  // same arithmetic as nms_gather_kernel
+    const float off = __fmul_rn((float)idxs[i], __fadd_rn(s_max, 1.f));
+    x1 = __fadd_rn(x1, off); y1 = __fadd_rn(y1, off);
+    x2 = __fadd_rn(x2, off); y2 = __fadd_rn(y2, off);
+  }
+  Box4f b;
+  b.x1 = x1; b.y1 = y1; b.x2 = x2; b.y2 = y2;
+  sorted[rank] = b;
+  if (sorted_cls) sorted_cls[rank] = (int32_t)idxs[i];
 }
 
 // ---- 4. IoU bit tiles ---------------------------------------------------------
@@ -906,8 +994,13 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
         (const int32_t*)L.idx_in, L.order, (int)n, 0, 64, st));
   } else if (n <= kSortMax) {
     if constexpr (!f64) {
-      nms_front_small_kernel<T><<<1, kSortThreads, 0, st>>>((const T*)boxes, (const T*)scores, idxs, (int)n, mode,
-                                                            (Box4f*)L.sorted, mode == 2 ? L.cls : nullptr, L.order);
+      const char* front = getenv("B200DET_NMS_FRONT");  // "block": the one-CTA block radix sort (read per call)
+      if (front && front[0] == 'b')
+        nms_front_small_kernel<T><<<1, kSortThreads, 0, st>>>((const T*)boxes, (const T*)scores, idxs, (int)n, mode,
+                                                              (Box4f*)L.sorted, mode == 2 ? L.cls : nullptr, L.order);
+      else
+        nms_front_rank_kernel<T><<<(int)((n + kRankKeys - 1) / kRankKeys), kRankThreads, (size_t)((n + 3) / 4) * 16, st>>>(
+            (const T*)boxes, (const T*)scores, idxs, (int)n, mode, (Box4f*)L.sorted, mode == 2 ? L.cls : nullptr, L.order);
     }
   } else {
     nms_prepare_kernel<T><<<bl, th, 0, st>>>((const T*)scores, n, (float*)L.keys_in, L.idx_in);

@@ -394,3 +394,35 @@ def test_sort_front_ends_agree_with_the_oracle_on_special_scores(capi, n):
         assert torch.equal(got.cpu(), oracle.batched_nms(b, s, idx, 0.5, name)), name
     bh, sh = b.half(), s.half()
     assert torch.equal(capi.nms(bh.to(DEV), sh.to(DEV), 0.5).cpu(), oracle.nms(bh.float(), sh.float(), 0.5))
+
+
+@pytest.mark.parametrize("n", [1, 3, 64, 65, 257, 5000, 8192])
+def test_front_ends_rank_sort_and_block_sort(capi, n, monkeypatch):
+    """The rank sort over all SMs (default for sets of up to 8192 boxes) and the one-CTA block radix sort
+    (B200DET_NMS_FRONT=block, read per call) must give the same keep list, which is the oracle's: tie runs,
+    signed zeros, infinities and NaN scores included (NaN sorts first, like torch's descending sort)."""
+    g = torch.Generator().manual_seed(100 + n)
+    b, _ = make_boxes(g, n, span=300.0)
+    s = torch.rand(n, generator=g)
+    s[::4] = 0.5
+    s[1::6] = 0.0
+    s[2::6] = -0.0
+    s[3::40] = float("inf")
+    s[5::40] = float("-inf")
+    s = s * torch.where(torch.rand(n, generator=g) < 0.3, -1.0, 1.0)
+    idx = torch.randint(0, 5, (n,), generator=g)
+    want = oracle.nms(b, s, 0.5)
+    wants = {name: oracle.batched_nms(b, s, idx, 0.5, name) for name in ("trick", "vanilla")}
+    sn = s.clone()
+    sn[7::31] = float("nan")
+    out = {}
+    for front in ("rank", "block"):
+        monkeypatch.setenv("B200DET_NMS_FRONT", front)
+        assert torch.equal(capi.nms(b.to(DEV), s.to(DEV), 0.5).cpu(), want), front
+        for mode, name in ((capi.BNMS_TRICK, "trick"), (capi.BNMS_VANILLA, "vanilla")):
+            got = capi.batched_nms(b.to(DEV), s.to(DEV), idx.to(DEV), 0.5, mode)
+            assert torch.equal(got.cpu(), wants[name]), (front, name)
+        out[front] = capi.nms(b.to(DEV), sn.to(DEV), 0.5).cpu()
+        bh, sh = b.half(), s.half()
+        assert torch.equal(capi.nms(bh.to(DEV), sh.to(DEV), 0.5).cpu(), oracle.nms(bh.float(), sh.float(), 0.5)), front
+    assert torch.equal(out["rank"], out["block"])
