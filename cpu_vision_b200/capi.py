@@ -29,7 +29,7 @@ SYMBOLS = [
     "b200det_nms_segmented_workspace_bytes", "b200det_nms_segmented", "b200det_clip_filter_boxes", "b200det_relayout",
     "b200det_roi_pool_forward", "b200det_roi_pool_backward", "b200det_ps_roi_pool_forward",
     "b200det_ps_roi_pool_backward", "b200det_ps_roi_align_forward", "b200det_ps_roi_align_backward",
-    "b200det_rpn_select", "b200det_roi_heads_decode",
+    "b200det_rpn_select", "b200det_roi_heads_decode", "b200det_nms_static",
 ]
 
 _declared = False
@@ -52,6 +52,7 @@ def lib():
         l.b200det_nms_workspace_bytes.restype = _S
         l.b200det_nms.argtypes = [_P, _P, _I, _L, _D, _P, _P, _P, _S, _P]
         l.b200det_batched_nms.argtypes = [_P, _P, _P, _I, _L, _D, _I, _P, _P, _P, _S, _P]
+        l.b200det_nms_static.argtypes = [_P, _P, _I, _L, _D, _P, _P, _P]
         l.b200det_roi_align_forward_host.argtypes = [_P, _I, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I, _I, _I]
         l.b200det_roi_align_backward_host.argtypes = [_P, _P, _L, _P, _P, _I, _I, _L, _L, _L, _L, _L, _L, _L, _D, _I,
                                                       _I, _I]
@@ -234,6 +235,25 @@ def nms(boxes, scores, iou_threshold, workspace: Optional[NmsWorkspace] = None, 
     if not sync:
         return w.keep, cnt
     return w.keep[: int(cnt.item())].clone()
+
+
+NMS_STATIC_MAX_BOXES = 8192  # B200DET_NMS_STATIC_MAX_BOXES (include/b200_detection_ops.h)
+
+
+def nms_static(boxes, scores, iou_threshold, keep, num_keep):
+    """b200det_nms_static: NMS on the library's built-in scratch array -- no allocation inside the call and no
+    workspace; the caller owns the outputs (`keep` int64 [>= N], `num_keep` int64 [1], both on the device) and
+    the inputs must already be contiguous and of one dtype.  At most NMS_STATIC_MAX_BOXES boxes; calls that
+    overlap on the GPU race on the shared scratch.  Asynchronous: nothing is read back here."""
+    n = boxes.shape[0]
+    if n and not (boxes.is_contiguous() and scores.is_contiguous() and scores.dtype == boxes.dtype):
+        raise ValueError("nms_static: contiguous boxes / scores of one dtype required (the call does not copy)")
+    if keep.dtype != torch.int64 or num_keep.dtype != torch.int64 or keep.numel() < n or num_keep.numel() < 1:
+        raise ValueError("nms_static: keep must be int64 [>= N] and num_keep int64 [1]")
+    with torch.cuda.device(boxes.device):
+        _check(lib().b200det_nms_static(boxes.data_ptr(), scores.data_ptr(), _dt(boxes), n, float(iou_threshold),
+                                        keep.data_ptr(), num_keep.data_ptr(), _stream(boxes)),
+               "b200det_nms_static")
 
 
 def batched_nms(boxes, scores, idxs, iou_threshold, mode=BNMS_AUTO, workspace: Optional[NmsWorkspace] = None,

@@ -19,6 +19,7 @@
 // comparison: inter / ((Sa + Sb) - inter) > (float)threshold.
 #include <stdlib.h>
 
+#include <mutex>
 #include <type_traits>
 #include <cub/block/block_radix_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
@@ -1523,3 +1524,61 @@ int nms_segmented_device(const void* boxes, const void* scores, const int64_t* i
 }
 
 }  // namespace b200det
+
+// ---- allocation-free NMS: b200det_nms_static ---------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) and do
+// not want to carry a workspace either: the same launch sequence as b200det_nms, with the scratch (sort keys,
+// order, score-ordered boxes, IoU bit mask) in a FIXED array that lives in the library's device image.  Every GPU
+// that loads the library holds B200DET_NMS_STATIC_BYTES (10 MiB) of it until the process exits; it fits sets of
+// up to B200DET_NMS_STATIC_MAX_BOXES (8192) boxes (8.9 MB: the bit mask is 8 MiB of it), larger sets are refused.
+// The array's name below is a host-side stand-in in host code, not a device address: the device address is taken
+// once per device, with that device current, through cudaGetSymbolAddress, and that pointer goes to the kernels.
+// Nothing in the scratch has to start at zero (every word the scan reads was written by this call's front end
+// or mask kernel), so it is not cleared; it keeps the last call's contents.  ALL calls on a device share the one
+// array: calls that overlap on the GPU (different streams, or graphs replayed concurrently) race; serialise them.
+static __device__ __align__(256) unsigned char g_nms_static_scratch[B200DET_NMS_STATIC_BYTES];
+
+namespace b200det {
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;
+void* g_static_ptr[kStaticMaxDevices] = {};
+
+int nms_static_scratch(void** out) {
+  int dev = -1;
+  B200DET_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kStaticMaxDevices) return fail(B200DET_ENOSUP, "nms_static: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (!g_static_ptr[dev]) {
+    void* p = nullptr;
+    B200DET_CUDA_OK(cudaGetSymbolAddress(&p, g_nms_static_scratch));
+    if (!p) return fail(B200DET_EINVAL, "nms_static: cudaGetSymbolAddress returned a null address");
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return 0;
+}
+}  // namespace
+}  // namespace b200det
+
+extern "C" int b200det_nms_static(const void* boxes, const void* scores, int dtype, int64_t N, double iou_threshold,
+                                  int64_t* keep, int64_t* num_keep, void* stream) {
+  using namespace b200det;
+  if (N < 0) return fail(B200DET_EINVAL, "nms_static: negative N");
+  if (!num_keep) return fail(B200DET_EINVAL, "nms_static: null num_keep");
+  if (N > 0 && (!boxes || !scores || !keep)) return fail(B200DET_EINVAL, "nms_static: null pointer");
+  if (dtype != B200DET_F32 && dtype != B200DET_F16 && dtype != B200DET_BF16 && dtype != B200DET_F64)
+    return fail(B200DET_ENOSUP, "nms_static: unknown dtype %d", dtype);
+  if (N > B200DET_NMS_STATIC_MAX_BOXES)
+    return fail(B200DET_EINVAL, "nms_static: N=%lld exceeds the built-in scratch (at most %d boxes); "
+                                "use b200det_nms with a caller-owned workspace", (long long)N, B200DET_NMS_STATIC_MAX_BOXES);
+  const size_t need = nms_workspace_bytes(N);
+  if (need > (size_t)B200DET_NMS_STATIC_BYTES)
+    return fail(B200DET_EWORKSPACE, "nms_static: N=%lld needs %zu bytes of scratch, the built-in array has %d",
+                (long long)N, need, B200DET_NMS_STATIC_BYTES);
+  void* scratch = nullptr;
+  const int rc = nms_static_scratch(&scratch);
+  if (rc != 0) return rc;
+  return nms_device(boxes, scores, nullptr, dtype, N, iou_threshold, 0, keep, num_keep, scratch,
+                    (size_t)B200DET_NMS_STATIC_BYTES, (cudaStream_t)stream);
+}

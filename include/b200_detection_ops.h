@@ -174,6 +174,20 @@ int b200det_nms(
     double iou_threshold, int64_t* keep, int64_t* num_keep, void* workspace,
     size_t workspace_bytes, void* stream);
 
+/* b200det_nms without ANY allocation and without a caller workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments, result and launch sequence as b200det_nms;
+ * the scratch is a fixed array in the library's device image (B200DET_NMS_STATIC_BYTES per GPU that loads the
+ * library, held until exit), which limits N to B200DET_NMS_STATIC_MAX_BOXES: a larger N returns B200DET_EINVAL
+ * with a message.  The call performs no cudaMalloc / cudaFree and calls no allocating library routine.  All
+ * calls on a device share the array (it keeps the last call's contents; nothing in it has to start at zero):
+ * calls that overlap on the GPU race -- keep them on one stream or order them with events. */
+#define B200DET_NMS_STATIC_MAX_BOXES 8192
+#define B200DET_NMS_STATIC_BYTES (10 * 1024 * 1024)
+int b200det_nms_static(
+    const void* boxes, const void* scores, int dtype, int64_t N,
+    double iou_threshold, int64_t* keep, int64_t* num_keep, void* stream);
+
 /* Class-aware NMS in one pass.  Replaces batched_nms
  * (torchvision/ops/boxes.py:44-112).
  *   idxs : device int64 [N] category of each box (the per-class compare of the VANILLA strategy and the
