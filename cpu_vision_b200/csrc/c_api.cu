@@ -82,6 +82,9 @@ static int forward_impl(const LevelArgs& lv, int dtype, const void* rois, const 
   int rc = roi_align_fwd_fast(lv, dtype, rois, levels, output, out_layout, K, (int)PH, (int)PW, sr,
                               aligned != 0, st, &taken);
   if (rc != 0 || taken) return rc;
+  rc = roi_align_fwd_anygrid(lv, dtype, rois, levels, output, out_layout, K, (int)PH, (int)PW, sr, aligned != 0, st,
+                             &taken);
+  if (rc != 0 || taken) return rc;
   return roi_align_fwd_generic(lv, dtype, rois, levels, output, out_layout, K, (int)PH, (int)PW, sr,
                                aligned != 0, st);
 }
@@ -144,6 +147,12 @@ static int backward_impl(const LevelArgs& lv, int dtype, const void* grad, const
     }
   }
   if (!work) return 0;
+  if (!deterministic) {  // any sampling grid on channels_last maps (adds into the gradients zeroed above)
+    int taken = 0;
+    const int rc = roi_align_bwd_anygrid(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr, aligned != 0, st,
+                                         &taken);
+    if (rc != 0 || taken) return rc;
+  }
   return roi_align_bwd_generic(lv, dtype, grad, gs, rois, levels, K, (int)PH, (int)PW, sr,
                                aligned != 0, st);
 }

@@ -43,6 +43,14 @@ int roi_align_bwd_fast(const LevelArgs& lv, int dtype, const void* grad, const i
                        const void* rois, const int32_t* levels, long long K, int PH, int PW,
                        int sr, bool aligned, bool zero_init, unsigned skip_levels, cudaStream_t st, int* taken);
 void roi_align_bwd_release();
+// roi_align_anygrid_sm100.cu: channels_last maps, any sampling grid (adaptive, > 2), C % 4 == 0: merged taps per
+// axis, a channel vector per lane.  The backward only ADDS: the caller zero-fills the gradients first.
+int roi_align_fwd_anygrid(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
+                          void* out, int out_layout, long long K, int PH, int PW, int sr,
+                          bool aligned, cudaStream_t st, int* taken);
+int roi_align_bwd_anygrid(const LevelArgs& lv, int dtype, const void* grad, const int64_t* gs,
+                          const void* rois, const int32_t* levels, long long K, int PH, int PW,
+                          int sr, bool aligned, cudaStream_t st, int* taken);
 // roi_align_bwd_strip_sm100.cu: write-once backward (a warp owns a strip of one feature row; shared-memory
 // accumulators, no atomics, no memset, deterministic); produces the levels named in level_mask (bit l) and
 // leaves the others untouched

@@ -73,8 +73,11 @@ void* cur_stream() { return (void*)at::cuda::getCurrentCUDAStream().stream(); }
 // and the RoIs are not a handful, an NCHW caller is served by relayout -> fast kernel -> relayout,
 // and still gets NCHW-contiguous results.  B200DET_NCHW_RELAYOUT=0 keeps the generic kernels.
 bool fast_shape(int dt, int64_t C, int64_t PH, int64_t PW, int64_t sr) {
-  return dt != B200DET_F64 && C > 0 && C % 128 == 0 && (sr == 1 || sr == 2) && PW >= 1 && PW * sr <= 32 &&
-         PH >= 1 && PH <= 32;
+  if (dt == B200DET_F64 || C <= 0 || PH < 1 || PW < 1) return false;
+  if (C % 128 == 0 && (sr == 1 || sr == 2) && PW * sr <= 32 && PH <= 32) return true;  // roi_align_{fwd,bwd}_sm100.cu
+  // roi_align_anygrid_sm100.cu: adaptive / larger sampling grids, C a multiple of 4
+  const char* e = getenv("B200DET_ANYGRID");
+  return (!e || atoi(e) != 0) && C >= 32 && C % 4 == 0 && PH <= 64 && PW <= 64;
 }
 bool relayout_pays(int64_t K, int64_t PH, int64_t PW, int64_t feature_pixels) {
   const char* e = getenv("B200DET_NCHW_RELAYOUT");  // read per call (the tests compare both paths in one process)
