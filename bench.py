@@ -577,9 +577,29 @@ def secondary_legs(capi, dev, peak):
     import cpu_vision_b200  # noqa: F401
 
     feats, rois, grad = make_cfg3(dev, torch.float32, 1237)
+    # cfg3 with the op's DEFAULT sampling_ratio (<= 0: adaptive grids, what torchvision.ops.roi_align(x, boxes, 14)
+    # and the reference's test_ops.py use): roi_align_anygrid_sm100.cu against the generic one-thread-per-element
+    # kernels (the reference's parallelisation, B200DET_ANYGRID=0) on the same channels_last tensors
+    lvl = capi.fpn_level_map(rois, 2, 5)
+    oa_ = torch.empty(rois.shape[0], C, 14, 14, device=dev).contiguous(memory_format=torch.channels_last)
+    ga_ = [torch.empty_like(f) for f in feats]
+    shp3 = [(16, C, h, w) for h, w in SHAPES]
+    ad = {}
+    for sw in ("1", "0"):
+        os.environ["B200DET_ANYGRID"] = sw
+        ad[sw] = (timed(lambda: capi.msroi_align_forward(feats, rois, SCALES, 14, 14, 0, False, levels=lvl, out=oa_),
+                        iters=5, flush_l2=False),
+                  timed(lambda: capi.msroi_align_backward(grad, rois, lvl, SCALES, shp3, 14, 14, 0, False,
+                                                          layout=capi.NHWC, outs=ga_), iters=5, flush_l2=False))
+    os.environ.pop("B200DET_ANYGRID", None)
+    res["cfg3_fp32_adaptive_sampling"] = {
+        "fwd_ms": ad["1"][0], "bwd_ms": ad["1"][1], "fwd_bwd_rois_per_s": rois.shape[0] / (sum(ad["1"]) / 1e3),
+        "generic_kernels_fwd_ms": ad["0"][0], "generic_kernels_bwd_ms": ad["0"][1],
+        "note": "sampling_ratio 0 (grid = ceil(roi / bins): 1-2 samples per bin and axis on these levels); bwd includes "
+                "the zero fill of the 1.18 GB gradient"}
+    del oa_, ga_
     fn, gn = [f.contiguous() for f in feats], grad.contiguous()
     del feats, grad
-    lvl = capi.fpn_level_map(rois, 2, 5)
     hs_, ws_ = [h for h, _ in SHAPES], [w for _, w in SHAPES]
     nf = timed(lambda: torch.ops.b200det.msroi_align(fn, rois, SCALES, 14, 14, 2, False, 2, 5, 224, 4, 1e-6), iters=5,
                flush_l2=False)

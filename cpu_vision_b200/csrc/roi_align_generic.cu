@@ -1,7 +1,8 @@
 // roi_align_generic.cu -- stride-addressed RoIAlign forward/backward for every
-// case the specialised sm_100a kernels (roi_align_fast.cu) do not take:
-// adaptive sampling (sampling_ratio <= 0), sampling_ratio > 2, fp64, NCHW
-// feature maps, channel counts that are not a multiple of the vector width.
+// case the sm_100a kernels (roi_align_{fwd,bwd}_sm100.cu: sampling_ratio 1 / 2, C % 128 == 0;
+// roi_align_anygrid_sm100.cu: any sampling grid, C % 4 == 0, both channels_last) do not take:
+// fp64, NCHW feature maps, channel counts below 32 or not a multiple of 4, gradients
+// that are not channel-contiguous.
 //
 // One thread per pooled output element, like the reference
 // (torchvision/csrc/ops/cuda/roi_align_kernel.cu:68-143, :204-332), but
