@@ -30,6 +30,8 @@ SYMBOLS = [
     "b200det_roi_pool_forward", "b200det_roi_pool_backward", "b200det_ps_roi_pool_forward",
     "b200det_ps_roi_pool_backward", "b200det_ps_roi_align_forward", "b200det_ps_roi_align_backward",
     "b200det_rpn_select", "b200det_roi_heads_decode", "b200det_nms_static",
+    "b200det_msroi_align_forward_push", "b200det_peer_alloc", "b200det_peer_free", "b200det_peer_export",
+    "b200det_peer_open", "b200det_peer_close",
 ]
 
 _declared = False
@@ -48,6 +50,13 @@ def lib():
                                                   _I, _I, _I, _I, _I, _I, _D, _P]
         l.b200det_msroi_align_backward.argtypes = [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _L, _L,
                                                    _I, _I, _I, _P]
+        l.b200det_msroi_align_forward_push.argtypes = [_P, _P, _P, _P, _I, _I, _P, _P, _I, _P, _P, _I, _I, _I, _L, _L,
+                                                       _L, _L, _L, _I, _I, _I, _I, _I, _I, _D, _P]
+        l.b200det_peer_alloc.argtypes = [_S, _P]
+        l.b200det_peer_free.argtypes = [_P]
+        l.b200det_peer_export.argtypes = [_P, _P]
+        l.b200det_peer_open.argtypes = [_P, _P]
+        l.b200det_peer_close.argtypes = [_P]
         l.b200det_nms_workspace_bytes.argtypes = [_L]
         l.b200det_nms_workspace_bytes.restype = _S
         l.b200det_nms.argtypes = [_P, _P, _I, _L, _D, _P, _P, _P, _S, _P]
@@ -192,6 +201,69 @@ def msroi_align_forward(feats: List[torch.Tensor], rois, scales, pooled_h, poole
                                                  canonical_scale, canonical_level, float(eps), _stream(f0)),
                "b200det_msroi_align_forward")
     return out, levels
+
+
+def msroi_align_forward_push(feats: List[torch.Tensor], rois, scales, pooled_h, pooled_w, sampling_ratio, out,
+                             peer_ptrs, aligned=False, k_min=2, k_max=5, canonical_scale=224, canonical_level=4,
+                             eps=1e-6, levels: Optional[torch.Tensor] = None):
+    """MultiScaleRoIAlign forward fused with the push all-gather: every pooled row is stored to `out` (this rank's
+    slice of its own gather buffer) and to the same row behind every pointer of `peer_ptrs` (this rank's slice of
+    the peers' buffers, device addresses as ints; sharding.PushGather owns them).  Returns (out, levels)."""
+    layout, f0 = _layout_of(feats[0])
+    if layout != NHWC:
+        raise ValueError("msroi_align_forward_push: channels_last features only")
+    feats = [f.contiguous(memory_format=torch.channels_last) for f in feats]
+    r = _arith(rois, f0.dtype)
+    N, Cc = f0.shape[:2]
+    K = r.shape[0]
+    if tuple(out.shape) != (K, Cc, pooled_h, pooled_w) or not out.is_contiguous(memory_format=torch.channels_last):
+        raise ValueError("msroi_align_forward_push: `out` must be a channels_last [K, C, PH, PW] tensor")
+    given = levels is not None
+    if not given:
+        levels = torch.empty(K, dtype=torch.int32, device=f0.device)
+    ptrs, hs, ws, sc = _level_arrays(feats, scales)
+    peers = (C.c_void_p * max(len(peer_ptrs), 1))(*[int(p) for p in peer_ptrs])
+    with torch.cuda.device(f0.device):
+        _check(lib().b200det_msroi_align_forward_push(ptrs, hs, ws, sc, len(feats), layout, r.data_ptr(),
+                                                      levels.data_ptr(), int(given), out.data_ptr(), peers,
+                                                      len(peer_ptrs), layout, _dt(f0), N, Cc, K, pooled_h, pooled_w,
+                                                      int(sampling_ratio), int(bool(aligned)), k_min, k_max,
+                                                      canonical_scale, canonical_level, float(eps), _stream(f0)),
+               "b200det_msroi_align_forward_push")
+    return out, levels
+
+
+def peer_alloc(nbytes: int, device) -> int:
+    """A cudaMalloc of its own on `device` (so that an IPC handle covers exactly it); returns the address."""
+    p = C.c_void_p(0)
+    with torch.cuda.device(device):
+        _check(lib().b200det_peer_alloc(int(nbytes), C.byref(p)), "b200det_peer_alloc")
+    return int(p.value)
+
+
+def peer_free(ptr: int, device):
+    with torch.cuda.device(device):
+        _check(lib().b200det_peer_free(C.c_void_p(ptr)), "b200det_peer_free")
+
+
+def peer_export(ptr: int, device) -> bytes:
+    h = C.create_string_buffer(64)
+    with torch.cuda.device(device):
+        _check(lib().b200det_peer_export(C.c_void_p(ptr), h), "b200det_peer_export")
+    return h.raw
+
+
+def peer_open(handle: bytes, device) -> int:
+    p = C.c_void_p(0)
+    h = C.create_string_buffer(handle, 64)
+    with torch.cuda.device(device):
+        _check(lib().b200det_peer_open(h, C.byref(p)), "b200det_peer_open")
+    return int(p.value)
+
+
+def peer_close(ptr: int, device):
+    with torch.cuda.device(device):
+        _check(lib().b200det_peer_close(C.c_void_p(ptr)), "b200det_peer_close")
 
 
 def msroi_align_backward(grad, rois, levels, scales, shapes, pooled_h, pooled_w, sampling_ratio, aligned=False,

@@ -75,13 +75,16 @@ static int fill_levels(const char* who, LevelArgs& lv, const void* const* feats,
 
 static int forward_impl(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
                         void* output, int out_layout, int64_t K, int64_t PH, int64_t PW, int sr,
-                        int aligned, cudaStream_t st) {
+                        int aligned, cudaStream_t st, const PeerOut* peers = nullptr) {
   if (K * lv.channels * PH * PW == 0) return 0;
   if (!rois || !output) return fail(B200DET_EINVAL, "roi_align forward: null pointer");
   int taken = 0;
   int rc = roi_align_fwd_fast(lv, dtype, rois, levels, output, out_layout, K, (int)PH, (int)PW, sr,
-                              aligned != 0, st, &taken);
+                              aligned != 0, st, &taken, peers);
   if (rc != 0 || taken) return rc;
+  if (peers && peers->n > 0)
+    return fail(B200DET_ENOSUP, "msroi_align_forward_push: only the channels_last fast path pushes (C %% 128 == 0, "
+                                "sampling_ratio 1 or 2, pooled_width * sampling_ratio <= 32, fp32 / fp16 / bf16)");
   rc = roi_align_fwd_anygrid(lv, dtype, rois, levels, output, out_layout, K, (int)PH, (int)PW, sr, aligned != 0, st,
                              &taken);
   if (rc != 0 || taken) return rc;
@@ -234,6 +237,81 @@ int b200det_msroi_align_forward(const void* const* feats, const int64_t* heights
   }
   return forward_impl(lv, dtype, rois, lv_ids, output, out_layout, K, PH, PW, sampling_ratio,
                       aligned, (cudaStream_t)stream);
+}
+
+int b200det_msroi_align_forward_push(const void* const* feats, const int64_t* heights,
+                                     const int64_t* widths, const double* scales, int num_levels,
+                                     int layout, const void* rois, int32_t* levels, int levels_given,
+                                     void* output, void* const* peer_outputs, int num_peers,
+                                     int out_layout, int dtype, int64_t N, int64_t C, int64_t K,
+                                     int64_t PH, int64_t PW, int sampling_ratio, int aligned, int k_min,
+                                     int k_max, int canonical_scale, int canonical_level, double eps,
+                                     void* stream) {
+  if (num_peers < 0 || num_peers > kMaxPeerOut)
+    return fail(B200DET_EINVAL, "msroi_align_forward_push: at most %d peer outputs", kMaxPeerOut);
+  if (num_peers > 0 && !peer_outputs) return fail(B200DET_EINVAL, "msroi_align_forward_push: null peer_outputs");
+  int rc = check_common("msroi_align_forward_push", dtype, layout, out_layout, N, C, K, PH, PW);
+  if (rc) return rc;
+  if (!feats || !heights || !widths || !scales)
+    return fail(B200DET_EINVAL, "msroi_align_forward_push: null level arrays");
+  PeerOut peers;
+  peers.n = num_peers;
+  for (int i = 0; i < num_peers; ++i) {
+    if (!peer_outputs[i] || ((uintptr_t)peer_outputs[i]) % 16 != 0)
+      return fail(B200DET_EINVAL, "msroi_align_forward_push: peer output %d is null or not 16-byte aligned", i);
+    peers.delta[i] = (long long)((const char*)peer_outputs[i] - (const char*)output);
+  }
+  LevelArgs lv;
+  rc = fill_levels("msroi_align_forward_push", lv, feats, heights, widths, scales, num_levels, layout, N, C);
+  if (rc) return rc;
+  const int32_t* lv_ids = nullptr;
+  if (num_levels > 1) {
+    if (K > 0 && !levels) return fail(B200DET_EINVAL, "msroi_align_forward_push: levels buffer required");
+    if (!levels_given && K > 0) {
+      rc = fpn_level_map(rois, dtype, K, k_min, k_max, canonical_scale, canonical_level, eps, levels,
+                         (cudaStream_t)stream);
+      if (rc) return rc;
+    }
+    lv_ids = levels;
+  } else if (levels && !levels_given && K > 0) {
+    B200DET_CUDA_OK(cudaMemsetAsync(levels, 0, (size_t)K * sizeof(int32_t), (cudaStream_t)stream));
+  }
+  return forward_impl(lv, dtype, rois, lv_ids, output, out_layout, K, PH, PW, sampling_ratio, aligned,
+                      (cudaStream_t)stream, &peers);
+}
+
+// ---- peer-visible device memory (CUDA IPC) for the push gather --------------------------------------------
+int b200det_peer_alloc(size_t bytes, void** ptr) {
+  if (!ptr || bytes == 0) return fail(B200DET_EINVAL, "peer_alloc: null pointer or zero size");
+  B200DET_CUDA_OK(cudaMalloc(ptr, bytes));
+  return 0;
+}
+
+int b200det_peer_free(void* ptr) {
+  if (ptr) B200DET_CUDA_OK(cudaFree(ptr));
+  return 0;
+}
+
+int b200det_peer_export(const void* ptr, void* handle) {
+  if (!ptr || !handle) return fail(B200DET_EINVAL, "peer_export: null pointer");
+  static_assert(sizeof(cudaIpcMemHandle_t) == B200DET_PEER_HANDLE_BYTES, "handle size");
+  cudaIpcMemHandle_t h;
+  B200DET_CUDA_OK(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
+  memcpy(handle, &h, sizeof(h));
+  return 0;
+}
+
+int b200det_peer_open(const void* handle, void** ptr) {
+  if (!ptr || !handle) return fail(B200DET_EINVAL, "peer_open: null pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  B200DET_CUDA_OK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+
+int b200det_peer_close(void* ptr) {
+  if (ptr) B200DET_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+  return 0;
 }
 
 int b200det_msroi_align_backward(const void* grad, const int64_t* grad_strides, const void* rois,

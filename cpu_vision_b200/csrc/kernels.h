@@ -31,11 +31,19 @@ int roi_align_bwd_generic(const LevelArgs& lv, int dtype, const void* grad, cons
 int fpn_level_map(const void* rois, int dtype, long long K, int k_min, int k_max, int s0, int lvl0,
                   double eps, int32_t* levels, cudaStream_t st);
 
+// Extra destinations of the forward's pooled rows (b200det_msroi_align_forward_push): byte offsets from `out` to
+// the same row in up to 7 other buffers -- peer GPUs' gather buffers mapped over NVLink.
+constexpr int kMaxPeerOut = 7;
+struct PeerOut {
+  long long delta[kMaxPeerOut];
+  int n;
+};
+
 // roi_align_fwd_sm100.cu / roi_align_bwd_sm100.cu: returns 1 when it took the call, 0 when the generic path
-// must run, <0 / >0 on error like the public API.
+// must run, <0 / >0 on error like the public API.  `peers` (may be null): every pooled bin is also stored there.
 int roi_align_fwd_fast(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels,
                        void* out, int out_layout, long long K, int PH, int PW, int sr,
-                       bool aligned, cudaStream_t st, int* taken);
+                       bool aligned, cudaStream_t st, int* taken, const PeerOut* peers = nullptr);
 // The backward zero-fills the gradients itself when zero_init is set (fused with the scatter).  Levels named in
 // skip_levels (bit l) are left alone: their RoIs are skipped and their maps not zero-filled (the strip kernel
 // produces them).

@@ -86,9 +86,20 @@ __device__ __forceinline__ void build_y(const RoiGeom<float>& g, int H, int row_
 }
 
 // ---- one pooled row -----------------------------------------------------------------------
-template <typename T, int CH, int SR, int NR>
+// a pooled bin leaves the SM: one streaming store to the output and, in the push variant, one more to the same row
+// of every peer buffer (peer GPUs' memory mapped over NVLink: the all-gather happens while the rows are produced)
+template <typename T, int CH, bool MULTI>
+__device__ __forceinline__ void store_bin(T* p, const float2 (&v)[CH / 2], const PeerOut& peers) {
+  PixVec<T, CH>::st(p, v);
+  if (MULTI) {
+    for (int d = 0; d < peers.n; ++d)
+      PixVec<T, CH>::st(reinterpret_cast<T*>(reinterpret_cast<char*>(p) + peers.delta[d]), v);
+  }
+}
+
+template <typename T, int CH, int SR, int NR, bool MULTI>
 __device__ __forceinline__ void sweep_row(const FwdTables& tb, const T* __restrict__ base, T* __restrict__ o,
-                                          int ph, int C, int SX) {
+                                          int ph, int C, int SX, const PeerOut& peers) {
   using PV = PixVec<T, CH>;
   constexpr int H2 = CH / 2;
   const T* rp[NR];
@@ -127,7 +138,7 @@ __device__ __forceinline__ void sweep_row(const FwdTables& tb, const T* __restri
         for (int i = 0; i < H2; ++i) acc[i] = __ffma2_rn(lx, hi[i], __ffma2_rn(hx, lo[i], acc[i]));
       }
       if (SR == 1 || (j & 1)) {
-        PV::st(o, acc);
+        store_bin<T, CH, MULTI>(o, acc, peers);
         o += C;
 #pragma unroll
         for (int i = 0; i < H2; ++i) acc[i] = make_float2(0.f, 0.f);
@@ -159,10 +170,10 @@ __device__ __forceinline__ void sweep_row(const FwdTables& tb, const T* __restri
   samples(SX, X, Y);  // nothing left unless the tables disagree; keeps every bin written
 }
 
-template <typename T, int CH, int SR>
+template <typename T, int CH, int SR, bool MULTI>
 __global__ void __launch_bounds__(128, sizeof(T) == 2 ? 5 : 4) roi_align_fwd_sm100_kernel(
     LevelTable<T> lv, const float* __restrict__ rois, const int32_t* __restrict__ levels, T* __restrict__ out,
-    int C, int PH, int PW, bool aligned, int CT) {
+    int C, int PH, int PW, bool aligned, int CT, const __grid_constant__ PeerOut peers) {
   __shared__ FwdTables tb;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ct = blockIdx.x % CT;
@@ -181,49 +192,55 @@ __global__ void __launch_bounds__(128, sizeof(T) == 2 ? 5 : 4) roi_align_fwd_sm1
   for (int ph = warp; ph < PH; ph += nwarps) {
     T* o = obase + (long long)ph * PW * C;
     switch (tb.y_nr[ph]) {
-      case 1: sweep_row<T, CH, SR, 1>(tb, base, o, ph, C, SX); break;
-      case 2: sweep_row<T, CH, SR, 2>(tb, base, o, ph, C, SX); break;
-      case 3: if (SR == 2) sweep_row<T, CH, SR, 3>(tb, base, o, ph, C, SX); break;
-      case 4: if (SR == 2) sweep_row<T, CH, SR, 4>(tb, base, o, ph, C, SX); break;
+      case 1: sweep_row<T, CH, SR, 1, MULTI>(tb, base, o, ph, C, SX, peers); break;
+      case 2: sweep_row<T, CH, SR, 2, MULTI>(tb, base, o, ph, C, SX, peers); break;
+      case 3: if (SR == 2) sweep_row<T, CH, SR, 3, MULTI>(tb, base, o, ph, C, SX, peers); break;
+      case 4: if (SR == 2) sweep_row<T, CH, SR, 4, MULTI>(tb, base, o, ph, C, SX, peers); break;
       default: {  // every y sample of the row is empty: the bins are zero
         float2 z[CH / 2];
 #pragma unroll
         for (int i = 0; i < CH / 2; ++i) z[i] = make_float2(0.f, 0.f);
-        for (int pw = 0; pw < PW; ++pw) PixVec<T, CH>::st(o + (long long)pw * C, z);
+        for (int pw = 0; pw < PW; ++pw) store_bin<T, CH, MULTI>(o + (long long)pw * C, z, peers);
       }
     }
   }
 }
 
-template <typename T, int CH>
+template <typename T, int CH, bool MULTI>
 int launch_fwd(const LevelArgs& lv, const void* rois, const int32_t* levels, void* out, long long K, int C, int PH,
-               int PW, int sr, bool aligned, cudaStream_t st) {
+               int PW, int sr, bool aligned, cudaStream_t st, const PeerOut& peers) {
   const LevelTable<T> tab = make_nhwc_table<T>(lv);
   const int CT = C / (32 * CH);
   const unsigned grid = (unsigned)(K * CT);
   const int nw = fwd_warps();
   if (sr == 1)
-    roi_align_fwd_sm100_kernel<T, CH, 1><<<grid, nw * 32, 0, st>>>(tab, (const float*)rois, levels, (T*)out, C,
-                                                                         PH, PW, aligned, CT);
+    roi_align_fwd_sm100_kernel<T, CH, 1, MULTI><<<grid, nw * 32, 0, st>>>(tab, (const float*)rois, levels, (T*)out,
+                                                                                C, PH, PW, aligned, CT, peers);
   else
-    roi_align_fwd_sm100_kernel<T, CH, 2><<<grid, nw * 32, 0, st>>>(tab, (const float*)rois, levels, (T*)out, C,
-                                                                         PH, PW, aligned, CT);
+    roi_align_fwd_sm100_kernel<T, CH, 2, MULTI><<<grid, nw * 32, 0, st>>>(tab, (const float*)rois, levels, (T*)out,
+                                                                                C, PH, PW, aligned, CT, peers);
   B200DET_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
 template <typename T>
 int launch_fwd_t(const LevelArgs& lv, const void* rois, const int32_t* levels, void* out, long long K, int C, int PH,
-                 int PW, int sr, bool aligned, cudaStream_t st) {
-  if (C % 256 == 0) return launch_fwd<T, 8>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st);
-  return launch_fwd<T, 4>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st);
+                 int PW, int sr, bool aligned, cudaStream_t st, const PeerOut* peers) {
+  PeerOut none;
+  none.n = 0;
+  if (peers && peers->n > 0) {
+    if (C % 256 == 0) return launch_fwd<T, 8, true>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st, *peers);
+    return launch_fwd<T, 4, true>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st, *peers);
+  }
+  if (C % 256 == 0) return launch_fwd<T, 8, false>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st, none);
+  return launch_fwd<T, 4, false>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st, none);
 }
 
 }  // namespace
 
 int roi_align_fwd_fast(const LevelArgs& lv, int dtype, const void* rois, const int32_t* levels, void* out,
                        int out_layout, long long K, int PH, int PW, int sr, bool aligned, cudaStream_t st,
-                       int* taken) {
+                       int* taken, const PeerOut* peers) {
   *taken = 0;
   if (!sm100_eligible(lv, dtype, PH, PW, sr) || out_layout != B200DET_NHWC) return 0;
   if (((uintptr_t)out) % 16 != 0) return 0;
@@ -232,9 +249,9 @@ int roi_align_fwd_fast(const LevelArgs& lv, int dtype, const void* rois, const i
   if (K * (C / 128) > 0x7fffffffLL) return 0;
   int rc = 0;
   switch (dtype) {
-    case B200DET_F32: rc = launch_fwd_t<float>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st); break;
-    case B200DET_F16: rc = launch_fwd_t<__half>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st); break;
-    case B200DET_BF16: rc = launch_fwd_t<__nv_bfloat16>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st); break;
+    case B200DET_F32: rc = launch_fwd_t<float>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st, peers); break;
+    case B200DET_F16: rc = launch_fwd_t<__half>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st, peers); break;
+    case B200DET_BF16: rc = launch_fwd_t<__nv_bfloat16>(lv, rois, levels, out, K, C, PH, PW, sr, aligned, st, peers); break;
     default: return 0;
   }
   if (rc) return rc;

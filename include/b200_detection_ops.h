@@ -134,6 +134,41 @@ int b200det_msroi_align_forward(
     int sampling_ratio, int aligned, int k_min, int k_max,
     int canonical_scale, int canonical_level, double eps, void* stream);
 
+/* MultiScaleRoIAlign forward FUSED with the all-gather of the pooled rows (a "push" gather over NVLink peer
+ * memory).  Replaces the pair the reference's multi-GPU recipes run after torchvision.ops on every rank,
+ *   out = MultiScaleRoIAlign(...)                       (torchvision/ops/poolers.py:289-327)
+ *   all_gather(out)                                     (references/detection/utils.py:82-106, dist.all_gather),
+ * with ONE kernel: every pooled bin is stored to `output` and, in the same instruction stream, to the same row of
+ * `peer_outputs[i]` -- the slice of THIS rank inside the gather buffer of peer GPU i, mapped into this process
+ * (b200det_peer_open below, or any peer-accessible pointer) -- so the rows travel while the next ones are computed
+ * and no separate collective pass reads them again.
+ *   peer_outputs : host array of num_peers (<= 7) device pointers, each 16-byte aligned, each [K, C, PH, PW] in
+ *                  `out_layout` like `output`
+ * Only the channels_last fast path pushes (C % 128 == 0, sampling_ratio 1 or 2, pooled_width * sampling_ratio <= 32,
+ * fp32 / fp16 / bf16, NHWC features and outputs); anything else returns B200DET_ENOSUP.  The caller orders the
+ * ranks around the call (a barrier before the peers' buffers are overwritten and one after the kernel, before anybody
+ * reads a gathered row): cpu_vision_b200/sharding.py PushGather does it with two stream-ordered 4-byte all-reduces. */
+int b200det_msroi_align_forward_push(
+    const void* const* feats, const int64_t* heights, const int64_t* widths,
+    const double* scales, int num_levels, int layout, const void* rois,
+    int32_t* levels, int levels_given, void* output, void* const* peer_outputs,
+    int num_peers, int out_layout, int dtype, int64_t N, int64_t C, int64_t K,
+    int64_t PH, int64_t PW, int sampling_ratio, int aligned, int k_min,
+    int k_max, int canonical_scale, int canonical_level, double eps,
+    void* stream);
+
+/* Peer-visible device memory for the push gather (CUDA IPC; the reference has no counterpart, NCCL owns its
+ * buffers there).  alloc / free: a cudaMalloc of its own, so that the handle covers exactly the buffer.  export:
+ * writes the B200DET_PEER_HANDLE_BYTES opaque bytes another process of this node passes to open, which maps the
+ * buffer into the caller's address space on its current device (peer access over NVLink is enabled lazily).
+ * close before the owner frees.  These are set-up calls: they allocate and synchronise. */
+#define B200DET_PEER_HANDLE_BYTES 64
+int b200det_peer_alloc(size_t bytes, void** ptr);
+int b200det_peer_free(void* ptr);
+int b200det_peer_export(const void* ptr, void* handle);
+int b200det_peer_open(const void* handle, void** ptr);
+int b200det_peer_close(void* ptr);
+
 /* MultiScaleRoIAlign backward: the autograd transpose of the call above.
  *   grad_feats[l] : device, logical [N, C, heights[l], widths[l]] in `layout`,
  *                   (flags as in b200det_roi_align_backward)

@@ -1,7 +1,9 @@
 """The exchange north_star names, on real GPUs over NCCL: images sharded by rank, roi_align forward written into
 each rank's slice of the gather buffer, NCCL all-gather of the pooled features and of the kept indices -- the
 result must equal the one-GPU result BIT FOR BIT (the reference has no such test: its only collectives live in
-references/detection/utils.py).  Needs >= 2 GPUs; skipped otherwise (gloo twin: tests/test_host_logic.py)."""
+references/detection/utils.py).  The fused variant (b200det_msroi_align_forward_push through sharding.PushGather:
+the forward kernel stores every pooled row into all ranks' buffers over NVLink peer memory) must leave the same
+bytes on every rank.  Needs >= 2 GPUs; skipped otherwise (gloo twin: tests/test_host_logic.py)."""
 import os
 import socket
 
@@ -56,6 +58,17 @@ def _worker(rank, world, port, images, per_img, ret):
         full, mine = sharding.gather_buffer(k_local, (256, 7, 7), torch.float32, dev, rank, world, torch.channels_last)
         capi.msroi_align_forward(my_feats, my_rois, SCALES, 7, 7, 2, False, k_min=3, k_max=5, out=mine)
         dist.all_gather_into_tensor(full, mine)
+        # the same exchange fused into the forward: every rank's kernel stores its rows into all ranks' buffers
+        pg = sharding.PushGather(k_local, 256, 7, 7, torch.float32, dev)
+        pushed, _ = pg.forward(my_feats, my_rois, SCALES, 7, 7, 2, False, k_min=3, k_max=5)
+        torch.cuda.synchronize()
+        push_ok = torch.equal(pushed, full)
+        pushed2, _ = pg.forward(my_feats, my_rois, SCALES, 7, 7, 2, False, k_min=3, k_max=5)  # buffer reuse
+        torch.cuda.synchronize()
+        push_ok = push_ok and torch.equal(pushed2, full)
+        flags = [None] * world
+        dist.all_gather_object(flags, bool(push_ok))
+        pg.close()
         kept = []
         for i in range(lo, hi):  # kept indices of this rank's images, gathered image by image
             keep = capi.batched_nms(boxes[i].to(dev), scores[i].to(dev), idxs[i].to(dev), 0.5)
@@ -73,6 +86,7 @@ def _worker(rank, world, port, images, per_img, ret):
                     ref = capi.batched_nms(boxes[i].to(dev), scores[i].to(dev), idxs[i].to(dev), 0.5)
                     ok = ok and torch.equal(kept[j][r], ref)
             ret["ok"] = bool(ok)
+            ret["push_ok"] = all(flags)
             ret["rows"] = int(full.shape[0])
         dist.barrier()
     finally:
@@ -91,4 +105,5 @@ def test_gathered_pooled_features_and_kept_indices_equal_the_one_gpu_result(worl
         ret = m.dict()
         mp.spawn(_worker, args=(world, _free_port(), images, per_img, ret), nprocs=world, join=True)
         assert ret.get("ok") is True, dict(ret)
+        assert ret.get("push_ok") is True, dict(ret)   # the fused forward + push gather, on every rank
         assert ret["rows"] == images * per_img
