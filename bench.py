@@ -359,6 +359,8 @@ def run_b200(args, rank, world, local):
         if world > 1:
             line["cfg4"] = cfg4["cfg4"]
             line["allgather"] = cfg4["allgather"]
+        torch.cuda.empty_cache()
+        line["cfg5"] = cfg5_leg(capi, dev, rank, world, dist)
         if rank == 0 and world == 1:
             line["secondary"] = secondary_legs(capi, dev, peak)
             line["secondary"]["cfg4_64img_x_2000"] = cfg4["cfg4"]
@@ -783,6 +785,74 @@ def cfg4_leg(capi, dev, rank, world, dist, peak):
         "limiter": "the all-gather: every GPU receives (N-1)/N of 6.42 GB over NVLink while the local kernels "
                    "take fwd_ms + bwd_ms"}
     return res
+
+
+def cfg5_leg(capi, dev, rank, world, dist):
+    """BASELINE.json configs[4] on its synthetic shapes at N GPUs: the post-backbone chain of
+    fasterrcnn_resnet50_fpn for 64 images of 800x1088 split 64 / N per rank (strong scaling, sharded by image, no
+    exchange): filter_proposals (5 levels x 3 anchors, 2000 / 2000, IoU 0.7) -> MultiScaleRoIAlign of the kept
+    proposals (7x7, 4 levels) -> postprocess_detections (91 classes, 0.05 / 0.5 / 100).  Device-timed, max over ranks."""
+    from cpu_vision_b200 import detection, sharding
+
+    B = 64
+    lo, hi = sharding.image_block(B, rank, world)
+    nb = hi - lo
+    gen = torch.Generator(device=dev).manual_seed(1234 + 5 + rank)
+    napl = [200 * 272 * 3, 100 * 136 * 3, 50 * 68 * 3, 25 * 34 * 3, 13 * 17 * 3]
+    A = sum(napl)
+    ctr = torch.rand(nb, A, 2, generator=gen, device=dev) * torch.tensor([1088.0, 800.0], device=dev)
+    wh = torch.exp(torch.rand(nb, A, 2, generator=gen, device=dev) * 3.5 + 2.5)
+    props = torch.cat([ctr - wh / 2, ctr + wh / 2], 2)
+    del ctr, wh
+    obj = torch.randn(nb * A, 1, generator=gen, device=dev)
+    shapes = [(800, 1088)] * nb
+    feats = [torch.randn(nb, C, h, w, generator=gen, device=dev).contiguous(memory_format=torch.channels_last)
+             for h, w in SHAPES]
+    P_, C_ = 1000, 91
+    lg = torch.randn(nb * P_, C_, generator=gen, device=dev) * 2.5
+    rg = torch.randn(nb * P_, C_ * 4, generator=gen, device=dev) * 0.5
+    state = {}
+
+    def rpn():
+        state["boxes"], _ = detection.filter_proposals(props, obj, shapes, napl, 2000, 2000, 0.7)
+
+    def pool():
+        bx = state["boxes"]
+        ids = torch.cat([torch.full((b.shape[0], 1), float(i), device=dev) for i, b in enumerate(bx)])
+        rois = torch.cat([ids, torch.cat(bx)], 1)
+        state["rois"] = rois.shape[0]
+        capi.msroi_align_forward(feats, rois, SCALES, 7, 7, 2, False)
+
+    def post():
+        # the box head runs between pooling and this step in the model; its outputs are synthetic here
+        detection.postprocess_detections(lg, rg, [b[:P_] if b.shape[0] >= P_ else torch.cat([b, b[:1].expand(P_ - b.shape[0], 4)])
+                                                  for b in state["boxes"]], shapes, 0.05, 0.5, 100)
+
+    def timed(fn, iters=5, warm=2):
+        for _ in range(warm):
+            fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        b.synchronize()
+        ms = a.elapsed_time(b) / iters
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms
+
+    r_ms, p_ms, d_ms = timed(rpn), timed(pool), timed(post)
+    return {"images": B, "images_per_rank": nb, "scaling": "strong", "filter_proposals_ms": r_ms,
+            "box_roi_pool_ms": p_ms, "rois_pooled_per_rank": state.get("rois"), "postprocess_detections_ms": d_ms,
+            "chain_ms": r_ms + p_ms + d_ms, "images_per_s": B / ((r_ms + p_ms + d_ms) / 1e3),
+            "note": "synthetic RPN / box-head outputs of the shapes fasterrcnn_resnet50_fpn produces for 800x1088 "
+                    "images; the reference's own model drives the same kernels at N = 1 in secondary.cfg5_model"}
 
 
 def gather_leg(out, world, dist):
