@@ -513,9 +513,12 @@ def test_msroi_align_host_entry_points_pipelined(golden, capi, channels_last, ch
 
 
 # ---- NCHW callers (the reference's default layout): relayout -> channels_last kernels -> relayout ---------
+@pytest.mark.parametrize("pipe", ["1", "0"])   # B200DET_RELAYOUT_PIPE: pipelined cp.async kernel / load-barrier-store kernels
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16, torch.float64])
-@pytest.mark.parametrize("shape", [(1, 1, 1, 1), (2, 3, 5, 7), (3, 256, 40, 56), (2, 130, 33, 65), (1, 64, 1, 200)])
-def test_relayout_both_ways(capi, dtype, shape):
+@pytest.mark.parametrize("shape", [(1, 1, 1, 1), (2, 3, 5, 7), (3, 256, 40, 56), (2, 130, 33, 65), (1, 64, 1, 200),
+                                   (2, 200, 24, 50), (70, 256, 14, 14), (40, 128, 7, 8), (300, 256, 7, 7)])
+def test_relayout_both_ways(capi, dtype, shape, pipe, monkeypatch):
+    monkeypatch.setenv("B200DET_RELAYOUT_PIPE", pipe)
     g = torch.Generator().manual_seed(sum(shape))
     x = torch.randn(shape, generator=g).to(dtype).to(DEV)
     cl = capi.relayout(x, True)
