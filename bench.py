@@ -336,6 +336,8 @@ def run_b200(args, rank, world, local):
     roofline = {
         "bound": "hbm", "kernel": f"msroi_align_{dom}", "achieved": achieved, "peak": peak, "unit": "GB/s",
         "frac": achieved / peak, "traffic": traffic.get(dom), "traffic_source": traffic.get("source"),
+        # the busiest unit of the dominant kernel in the same ncu capture: the SM -> L2 request port
+        "sm_l2_port": traffic.get(dom + "_sm_l2_port"),
         "peak_source": peak_src, "algorithmic_bytes_per_launch": algo[dom],
         "fwd": {"ms": fwd_ms, "GBps": algo["fwd"] / (fwd_ms / 1e3) / 1e9, "frac": algo["fwd"] / (fwd_ms / 1e3) / 1e9 / peak},
         "bwd": {"ms": bwd_ms, "GBps": algo["bwd"] / (bwd_ms / 1e3) / 1e9, "frac": algo["bwd"] / (bwd_ms / 1e3) / 1e9 / peak},

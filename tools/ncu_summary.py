@@ -19,6 +19,10 @@ KEYS = [
     "lts__t_sectors_srcunit_tex_op_red_lookup_miss.sum", "lts__d_atomic_input_cycles_active.avg.pct_of_peak_sustained_elapsed",
     "l1tex__t_sector_hit_rate.pct", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
     "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed",
+    # the SM -> L2 request port (what bounds the scatter backward)
+    "l1tex__m_l1tex2xbar_req_cycles_active.avg.pct_of_peak_sustained_elapsed",
+    "l1tex__m_l1tex2xbar_req_cycles_active.max.pct_of_peak_sustained_elapsed",
+    "l1tex__m_l1tex2xbar_write_bytes.sum",
     "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
     "sm__throughput.avg.pct_of_peak_sustained_elapsed",
     "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
@@ -114,11 +118,21 @@ def traffic(rep, workload, out_txt):
     hdr, units = rows[0], rows[1]
     ir, iw, iname = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
     res = {}
+    port = ["l1tex__m_l1tex2xbar_req_cycles_active.avg.pct_of_peak_sustained_elapsed",
+            "l1tex__m_l1tex2xbar_req_cycles_active.max.pct_of_peak_sustained_elapsed",
+            "l1tex__m_l1tex2xbar_write_bytes.sum"]
     for r in rows[2:]:
         name = r[iname]
         key = "fwd" if "fwd" in name else ("bwd" if "bwd" in name else None)
         if key and key not in res:
             res[key] = int(float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]])
+            if all(m in hdr for m in port):
+                # the SM -> L2 request port of the same launch: busy cycles (avg / busiest SM, %) and bytes through it
+                ib = hdr.index(port[2])
+                res[key + "_sm_l2_port"] = {
+                    "req_cycles_active_avg_pct": float(r[hdr.index(port[0])]),
+                    "req_cycles_active_max_pct": float(r[hdr.index(port[1])]),
+                    "write_bytes": int(float(r[ib]) * scale[units[ib]])}
     res["source"] = f"{out_txt} (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch; written by tools/ncu_summary.py --traffic)"
     path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "traffic.json")
     try:
