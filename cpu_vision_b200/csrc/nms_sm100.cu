@@ -42,6 +42,12 @@ __host__ __device__ __forceinline__ long long tri_base(int b, int cb) {
   return (long long)kTile * ((long long)b * cb - (long long)b * (b - 1) / 2);
 }
 
+// nms_resolve_kernel (section 5b): sets of up to kResolveMaxBlocks * 64 boxes, at most kResolveIters rounds
+constexpr int kResolveMaxBlocks = 128;
+constexpr int kResolveThreads = 256;
+constexpr int kResolveIters = 24;
+constexpr int kResolveCtlWords = 32;  // [1] CTAs done, [2] fail flag
+
 // Class-grouped sets cut every block row at its last live tile jmax[b] (nothing right of it can hold a bit):
 // row stride jmax[b] - b + 1, block bases from a prefix sum (wbase, in units of 64 words).  jmax == nullptr
 // is the plain triangular layout.
@@ -538,10 +544,16 @@ template <typename BoxT>
 __global__ void __launch_bounds__(kTile) nms_mask_kernel(int n, float thr,
                                                          const BoxT* __restrict__ boxes,
                                                          const int32_t* __restrict__ cls,
-                                                         u64* __restrict__ mask) {
+                                                         u64* __restrict__ mask, unsigned* __restrict__ resolve_ctl,
+                                                         u64* __restrict__ resolve_k) {
   pdl_launch_dependents();
   pdl_wait();  // (before the early exit too: the grid must not complete before its predecessor has)
   const int row_start = blockIdx.y, col_group = blockIdx.x;
+  // nms_resolve_kernel starts from "nothing decided": its control words and its kept / removed words are zero
+  if (resolve_ctl && row_start == 0 && col_group == 0) {
+    if (threadIdx.x < kResolveCtlWords) resolve_ctl[threadIdx.x] = 0u;
+    for (int w = threadIdx.x; w < 2 * ((n + kTile - 1) / kTile); w += kTile) resolve_k[w] = 0ULL;
+  }
   if (row_start > col_group * kColTiles + kColTiles - 1) return;
   mask_tiles<BoxT>(n, thr, boxes, cls, mask, row_start, col_group);
 }
@@ -845,10 +857,155 @@ __device__ __forceinline__ void scan_smem_body(
   finish_keep(keptw, remv, col_blocks, rank, order, keep, num_keep, s_base, &s_kept, top_n);
 }
 
+// ---- 5b. the greedy result by monotone propagation, on all SMs -------------------------------------
+// A box is FINALLY REMOVED once one of its suppressors (a higher-ranked box with an IoU bit towards it) is finally
+// kept, and FINALLY KEPT once all of its suppressors are finally removed; boxes without suppressors start out kept.
+// Both sets only grow, their limit is the greedy result (the dependence is strictly upper-triangular), and a box
+// is decided after as many rounds as its longest suppression chain is deep -- a handful for real detections.
+// One CTA per 64-box column block j keeps ITS column of the bit mask in shared memory (the words (i, j) of all rows
+// i < 64 (j + 1), diagonal words cut to the bits right of the row).  A round reads the published kept / removed
+// words of the blocks left of it (plain L2 loads: the sets are monotone, so stale words only delay, and no barrier
+// or fence orders the CTAs), ORs the rows that are finally kept (-> removed bits) and the rows that are not yet
+// finally removed (-> still threatened bits), closes the chains INSIDE its own 64 boxes with a warp-level fixed
+// point, and publishes its two words.  A CTA whose 64 boxes are decided waits for the blocks left of it, compacts
+// its kept boxes into keep[] (prefix of popcounts) and counts itself done; the scan kernel behind returns at once
+// when all CTAs are.  A CTA that is not decided after kResolveIters rounds (suppression chains deeper than
+// that across blocks) raises the fail flag: everybody leaves and the serial scan kernel does the work as before --
+// the result is the same either way.  Replaces the host-side scan of the reference (cuda/nms_kernel.cu:136-159).
+// ctl: [1] CTAs done, [2] fail flag.
+__device__ __forceinline__ u64 ld_l2_u64(const u64* p) {  // from L2, never hoisted or merged by the compiler
+  u64 v;
+  asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned ld_l2_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(kResolveThreads) nms_resolve_kernel(
+    const u64* __restrict__ mask, int n, int cb, const int32_t* __restrict__ order, int64_t* __restrict__ keep,
+    int64_t* __restrict__ num_keep, u64* __restrict__ kw /* [2][cb]: kept, removed */, unsigned* __restrict__ ctl) {
+  pdl_launch_dependents();
+  pdl_wait();  // the mask is complete, the control words are zero
+  extern __shared__ __align__(16) u64 smem[];
+  u64* col = smem;                          // [(j + 1) * 64] words of this column
+  u64* skf = smem + (size_t)cb * kTile;     // [cb] published kept words
+  u64* srf = skf + cb;                      // [cb] published removed words
+  __shared__ u64 s_red[2][kResolveThreads / 32];
+  __shared__ u64 s_pub[2];
+  __shared__ int s_state;                   // 0 go on, 1 decided, 2 give up
+  const int j = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  u64* gkf = kw;
+  u64* grf = kw + cb;
+  const int tail = n - j * kTile;
+  const u64 alive = tail >= kTile ? ~0ULL : ((1ULL << tail) - 1ULL);
+  // boxes past the end count as removed; nothing is kept yet (the mask kernel left all published words zero:
+  // "undecided", which a reader treats as a threat that has not gone away yet)
+  if (tid == 0) __stcg(grf + j, ~alive);
+  const int nent = (j + 1) * kTile;
+  for (int e = tid; e < nent; e += kResolveThreads) {
+    const int b = e >> 6, r = e & 63;
+    u64 w = __ldcg(mask + tri_base(b, cb) + (long long)r * (cb - b) + (j - b));
+    if (b == j) w &= ~((2ULL << r) - 1ULL);  // diagonal word: bits right of the row only (row 63: none)
+    col[e] = w;
+  }
+  u64 kf = 0, rf = ~alive;   // this block's decided bits (uniform across the CTA after every round)
+  __syncthreads();
+  const int r = tid & 63;
+  for (int round = 0;; ++round) {
+    for (int b = tid; b < j; b += kResolveThreads) {
+      skf[b] = ld_l2_u64(gkf + b);
+      srf[b] = ld_l2_u64(grf + b);
+    }
+    __syncthreads();
+    // rows of the blocks left of this one: thread tid owns row tid % 64 of blocks tid / 64, tid / 64 + 4, ...
+    u64 a = 0, t = 0;  // a: bits removed by a finally kept row; t: bits still threatened by a row not yet removed
+    for (int b = tid >> 6; b < j; b += kResolveThreads / kTile) {
+      const u64 w = col[b * kTile + r];
+      a |= ((skf[b] >> r) & 1ULL) ? w : 0ULL;
+      t |= ((srf[b] >> r) & 1ULL) ? 0ULL : w;
+    }
+    {
+      const unsigned alo = __reduce_or_sync(0xffffffffu, (unsigned)a), ahi = __reduce_or_sync(0xffffffffu, (unsigned)(a >> 32));
+      const unsigned tlo = __reduce_or_sync(0xffffffffu, (unsigned)t), thi = __reduce_or_sync(0xffffffffu, (unsigned)(t >> 32));
+      if (lane == 0) {
+        s_red[0][warp] = ((u64)ahi << 32) | alo;
+        s_red[1][warp] = ((u64)thi << 32) | tlo;
+      }
+    }
+    __syncthreads();
+    if (warp == 0) {
+      u64 aoff = 0, toff = 0;
+#pragma unroll
+      for (int w = 0; w < kResolveThreads / 32; ++w) { aoff |= s_red[0][w]; toff |= s_red[1][w]; }
+      // the chains inside the block: lane l holds diagonal rows l and l + 32
+      const u64 d0 = col[j * kTile + lane], d1 = col[j * kTile + lane + 32];
+      u64 nk = kf, nr = rf;
+      for (;;) {
+        u64 av = ((nk >> lane) & 1ULL) ? d0 : 0ULL, tv = ((nr >> lane) & 1ULL) ? 0ULL : d0;
+        av |= ((nk >> (lane + 32)) & 1ULL) ? d1 : 0ULL;
+        tv |= ((nr >> (lane + 32)) & 1ULL) ? 0ULL : d1;
+        const u64 ad = ((u64)__reduce_or_sync(0xffffffffu, (unsigned)(av >> 32)) << 32) | __reduce_or_sync(0xffffffffu, (unsigned)av);
+        const u64 td = ((u64)__reduce_or_sync(0xffffffffu, (unsigned)(tv >> 32)) << 32) | __reduce_or_sync(0xffffffffu, (unsigned)tv);
+        const u64 r2 = nr | ((aoff | ad) & alive);
+        const u64 k2 = nk | (alive & ~(toff | td) & ~r2);
+        if (r2 == nr && k2 == nk) break;
+        nr = r2;
+        nk = k2;
+      }
+      if (lane == 0) {
+        if (nk != kf) __stcg(gkf + j, nk);
+        if (nr != rf) __stcg(grf + j, nr);
+        s_pub[0] = nk;
+        s_pub[1] = nr;
+        int st = (nk | nr) == ~0ULL ? 1 : 0;
+        if (!st && (round + 1 >= kResolveIters || ld_l2_u32(ctl + 2))) {
+          st = 2;
+          __stcg(ctl + 2, 1u);
+        }
+        s_state = st;
+      }
+    }
+    __syncthreads();
+    kf = s_pub[0];
+    rf = s_pub[1];
+    if (s_state == 2) return;  // the scan kernel takes over
+    if (s_state == 1) break;
+  }
+  // decided: kf is this block's part of the greedy result.  Its position in keep[] needs the blocks left of it.
+  for (int b = tid; b < j; b += kResolveThreads) {
+    u64 k = 0;
+    for (int spins = 0;; ++spins) {
+      k = ld_l2_u64(gkf + b);
+      if ((k | ld_l2_u64(grf + b)) == ~0ULL) break;
+      if ((spins & 15) == 15 && ld_l2_u32(ctl + 2)) break;  // somebody gave up: the flag is checked below
+      __nanosleep(100);
+    }
+    skf[b] = k;
+  }
+  __syncthreads();
+  if (tid == 0) s_state = ld_l2_u32(ctl + 2) ? 2 : 1;  // one reader: the CTA leaves or stays as a whole
+  __syncthreads();
+  if (s_state == 2) return;
+  int before = 0;
+  for (int b = lane; b < j; b += 32) before += __popcll(skf[b]);
+  before = __reduce_add_sync(0xffffffffu, before);  // every warp computes the same prefix
+  if (tid < kTile && ((kf >> tid) & 1ULL))
+    keep[before + __popcll(kf & ((1ULL << tid) - 1ULL))] = (int64_t)order[j * kTile + tid];
+  if (tid == 0) {
+    if (j == cb - 1) *num_keep = before + __popcll(kf);
+    atomicAdd(ctl + 1, 1u);  // read by the scan kernel after this grid has completed
+  }
+}
+
 __global__ void __launch_bounds__(kSmemThreads) nms_scan_smem_kernel(
     const u64* __restrict__ mask, int n, int col_blocks, const int32_t* __restrict__ order,
-    int64_t* __restrict__ keep, int64_t* __restrict__ num_keep) {
+    int64_t* __restrict__ keep, int64_t* __restrict__ num_keep, const unsigned* __restrict__ resolve_ctl) {
   pdl_wait();
+  // every CTA of nms_resolve_kernel decided its boxes and wrote its part of keep[]: nothing left to do
+  if (resolve_ctl && __ldcg(resolve_ctl + 1) == (unsigned)col_blocks && !__ldcg(resolve_ctl + 2)) return;
   scan_smem_body(mask, n, col_blocks, order, keep, num_keep, nullptr, 0);
 }
 
@@ -956,6 +1113,8 @@ struct Layout {
   void *keys_in, *keys_out, *cub_tmp, *sorted, *maxc;
   int32_t *idx_in, *order, *cls;
   u64* mask;
+  u64* resolve_k;          // [2][col_blocks] K words of nms_resolve_kernel
+  unsigned* resolve_ctl;   // kResolveCtlWords control words
   size_t cub_bytes, total;
 };
 
@@ -975,6 +1134,8 @@ Layout carve(void* ws, long long n) {
   if (f32b > L.cub_bytes) L.cub_bytes = f32b;
   L.cub_tmp = c.take(L.cub_bytes);
   L.mask = (u64*)c.take((size_t)n * cb * 8);
+  L.resolve_k = (u64*)c.take((size_t)2 * cb * 8);
+  L.resolve_ctl = (unsigned*)c.take(kResolveCtlWords * 4);
   L.total = c.off + 256;
   return L;
 }
@@ -1016,14 +1177,25 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
                                             (BoxT*)L.sorted, mode == 2 ? L.cls : nullptr);
   }
   dim3 grid((col_blocks + kColTiles - 1) / kColTiles, col_blocks);
+  // B200DET_NMS_RESOLVE=0 (read per call) keeps the serial scan alone
+  const char* res_s = getenv("B200DET_NMS_RESOLVE");
+  const bool resolve = col_blocks >= 2 && col_blocks <= kResolveMaxBlocks && !(res_s && atoi(res_s) == 0);
+  unsigned* ctl = resolve ? L.resolve_ctl : nullptr;
   B200DET_CUDA_OK(launch_pdl(nms_mask_kernel<BoxT>, grid, dim3(kTile), 0, st, (int)n, (float)thr, (const BoxT*)L.sorted,
-                             (const int32_t*)(mode == 2 ? L.cls : nullptr), L.mask));
+                             (const int32_t*)(mode == 2 ? L.cls : nullptr), L.mask, ctl, L.resolve_k));
+  if (resolve) {
+    const size_t rsmem = ((size_t)col_blocks * kTile + 2 * (size_t)col_blocks) * sizeof(u64);
+    if (rsmem > 48 * 1024)
+      B200DET_CUDA_OK(cudaFuncSetAttribute(nms_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));
+    B200DET_CUDA_OK(launch_pdl(nms_resolve_kernel, dim3(col_blocks), dim3(kResolveThreads), rsmem, st, (const u64*)L.mask,
+                               (int)n, col_blocks, (const int32_t*)L.order, keep, num_keep, L.resolve_k, ctl));
+  }
   if (col_blocks <= kSmemBlocks) {
     const size_t smem = ((size_t)(kRowGroups + 1) * col_blocks + 1 + kDiagRing * kTile + (size_t)2 * kTile * col_blocks) * sizeof(u64);
     if (smem > 48 * 1024)
       B200DET_CUDA_OK(cudaFuncSetAttribute(nms_scan_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     B200DET_CUDA_OK(launch_pdl(nms_scan_smem_kernel, dim3(1), dim3(kSmemThreads), smem, st, (const u64*)L.mask, (int)n,
-                               col_blocks, (const int32_t*)L.order, keep, num_keep));
+                               col_blocks, (const int32_t*)L.order, keep, num_keep, (const unsigned*)ctl));
   } else {
     const size_t smem = (size_t)col_blocks * 16;
     if (smem > 48 * 1024)

@@ -426,3 +426,42 @@ def test_front_ends_rank_sort_and_block_sort(capi, n, monkeypatch):
         bh, sh = b.half(), s.half()
         assert torch.equal(capi.nms(bh.to(DEV), sh.to(DEV), 0.5).cpu(), oracle.nms(bh.float(), sh.float(), 0.5)), front
     assert torch.equal(out["rank"], out["block"])
+
+
+# ---- the fixed-point resolve kernel (all SMs) and its fall-back to the serial scan --------------------------
+def _chain(n, kind, w=10.0, h=10.0):
+    """Boxes on a line, scores descending with the index.
+    deep:     box i shifted by 2 i: IoU(i, i + 1) = 8/12 > 0.5 and IoU(i, i + 2) = 6/14 < 0.5, so the greedy result
+              alternates kept / removed down the line -- a suppression chain as deep as the set.
+    clusters: groups of 5 boxes one unit apart (IoU 0.82, 0.67, 0.54, 0.43 with the first), groups far apart: box 0
+              of a group removes 1-3, box 4 survives only because they are gone -- depth 2 everywhere."""
+    i = torch.arange(n, dtype=torch.float32)
+    x = i * 2.0 if kind == "deep" else torch.floor(i / 5) * 100.0 + torch.remainder(i, 5) * 1.0
+    boxes = torch.stack([x, torch.zeros(n), x + w, torch.full((n,), h)], 1)
+    scores = torch.linspace(1.0, 0.5, n)
+    return boxes, scores
+
+
+@pytest.mark.parametrize("resolve", ["1", "0"])   # B200DET_NMS_RESOLVE: fixed point on all SMs first / serial scan alone
+@pytest.mark.parametrize("kind", ["deep", "clusters"])
+@pytest.mark.parametrize("n", [9, 130, 3000, 8192])
+def test_suppression_chains_resolve_kernel_and_fallback(capi, n, kind, resolve, monkeypatch):
+    """Deep chains need ~n/2 rounds of the fixed-point iteration, far beyond the resolve kernel's limit: the serial
+    scan must take over.  Clusters are finished by the resolve kernel itself.  Same keep indices as the oracle
+    either way, also when the chains sit among random boxes of several classes (both batched strategies)."""
+    monkeypatch.setenv("B200DET_NMS_RESOLVE", resolve)
+    boxes, scores = _chain(n, kind)
+    keep = capi.nms(boxes.to(DEV), scores.to(DEV), 0.5)
+    want = oracle.nms(boxes, scores, 0.5)
+    assert torch.equal(keep.cpu(), want)
+    assert want.numel() == ((n + 1) // 2 if kind == "deep" else 2 * (n // 5) + min(n % 5, 1))
+    g = torch.Generator().manual_seed(n)
+    m = min(n, 2000)
+    xy = torch.rand(m, 2, generator=g) * 300
+    rb = torch.cat([xy, xy + torch.rand(m, 2, generator=g) * 60 + 5], 1)
+    k = min(n, 8192 - m)
+    ab, asc = torch.cat([boxes[:k], rb]), torch.cat([scores[:k], torch.rand(m, generator=g)])
+    idxs = torch.randint(0, 3, (ab.shape[0],), generator=g)
+    for mode in (capi.BNMS_TRICK, capi.BNMS_VANILLA):
+        keep = capi.batched_nms(ab.to(DEV), asc.to(DEV), idxs.to(DEV), 0.5, mode)
+        assert torch.equal(keep.cpu(), oracle.batched_nms(ab, asc, idxs, 0.5, "trick" if mode == capi.BNMS_TRICK else "vanilla"))
