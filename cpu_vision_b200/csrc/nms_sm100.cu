@@ -42,8 +42,9 @@ __host__ __device__ __forceinline__ long long tri_base(int b, int cb) {
   return (long long)kTile * ((long long)b * cb - (long long)b * (b - 1) / 2);
 }
 
-// nms_resolve_kernel (section 5b): sets of up to kResolveMaxBlocks * 64 boxes, at most kResolveIters rounds
-constexpr int kResolveMaxBlocks = 128;
+// nms_resolve_kernel (section 5b): sets of up to kResolveMaxBlocks * 64 = 13312 boxes (110 KB of shared memory per
+// CTA there: two CTAs per SM, so all 208 are resident at once), at most kResolveIters rounds
+constexpr int kResolveMaxBlocks = 208;
 constexpr int kResolveThreads = 256;
 constexpr int kResolveIters = 24;
 constexpr int kResolveCtlWords = 32;  // [1] CTAs done, [2] fail flag

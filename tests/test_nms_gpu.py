@@ -444,7 +444,7 @@ def _chain(n, kind, w=10.0, h=10.0):
 
 @pytest.mark.parametrize("resolve", ["1", "0"])   # B200DET_NMS_RESOLVE: fixed point on all SMs first / serial scan alone
 @pytest.mark.parametrize("kind", ["deep", "clusters"])
-@pytest.mark.parametrize("n", [9, 130, 3000, 8192])
+@pytest.mark.parametrize("n", [9, 130, 3000, 8192, 13312])
 def test_suppression_chains_resolve_kernel_and_fallback(capi, n, kind, resolve, monkeypatch):
     """Deep chains need ~n/2 rounds of the fixed-point iteration, far beyond the resolve kernel's limit: the serial
     scan must take over.  Clusters are finished by the resolve kernel itself.  Same keep indices as the oracle

@@ -10,7 +10,7 @@ def timed(fn, iters=200):
     for _ in range(iters): fn()
     b.record(); b.synchronize()
     return a.elapsed_time(b) / iters
-for n in (1000, 2000, 5000, 8192):
+for n in (1000, 2000, 5000, 8192, 8663, 13312):
     gen = torch.Generator(device=dev).manual_seed(1236)
     xy = torch.rand(n, 2, generator=gen, device=dev) * 1000
     boxes = torch.cat([xy, xy + torch.rand(n, 2, generator=gen, device=dev) * 200 + 10], 1)
