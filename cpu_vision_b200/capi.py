@@ -31,7 +31,7 @@ SYMBOLS = [
     "b200det_ps_roi_pool_backward", "b200det_ps_roi_align_forward", "b200det_ps_roi_align_backward",
     "b200det_rpn_select", "b200det_roi_heads_decode", "b200det_nms_static",
     "b200det_msroi_align_forward_push", "b200det_peer_alloc", "b200det_peer_free", "b200det_peer_export",
-    "b200det_peer_open", "b200det_peer_close",
+    "b200det_peer_open", "b200det_peer_close", "b200det_segmented_topk",
 ]
 
 _declared = False
@@ -52,6 +52,7 @@ def lib():
                                                    _I, _I, _I, _P]
         l.b200det_msroi_align_forward_push.argtypes = [_P, _P, _P, _P, _I, _I, _P, _P, _I, _P, _P, _I, _I, _I, _L, _L,
                                                        _L, _L, _L, _I, _I, _I, _I, _I, _I, _D, _P]
+        l.b200det_segmented_topk.argtypes = [_P, _L, _L, _P, _I, _L, _P, _L, _P]
         l.b200det_peer_alloc.argtypes = [_S, _P]
         l.b200det_peer_free.argtypes = [_P]
         l.b200det_peer_export.argtypes = [_P, _P]
@@ -231,6 +232,27 @@ def msroi_align_forward_push(feats: List[torch.Tensor], rois, scales, pooled_h, 
                                                       canonical_scale, canonical_level, float(eps), _stream(f0)),
                "b200det_msroi_align_forward_push")
     return out, levels
+
+
+SEGMENTED_TOPK_MAX_K = 2048
+
+
+def segmented_topk(scores, num_anchors_per_level, k):
+    """scores fp32 [B, A] -> int64 [B, sum(min(k, n_l))]: per level the indices (into A) of its top-k scores in
+    descending order, ties by ascending index (b200det_segmented_topk; rpn.py:231-240 in one launch)."""
+    s = scores.contiguous()
+    B, A = s.shape
+    ends, acc = [], 0
+    for n in num_anchors_per_level:
+        acc += int(n)
+        ends.append(acc)
+    P = sum(min(int(k), int(n)) for n in num_anchors_per_level)
+    out = torch.empty((B, P), dtype=torch.int64, device=s.device)
+    le = (C.c_int32 * len(ends))(*ends)
+    with torch.cuda.device(s.device):
+        _check(lib().b200det_segmented_topk(s.data_ptr(), B, A, le, len(ends), int(k), out.data_ptr(), P, _stream(s)),
+               "b200det_segmented_topk")
+    return out
 
 
 def peer_alloc(nbytes: int, device) -> int:

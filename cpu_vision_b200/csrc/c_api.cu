@@ -431,6 +431,12 @@ int b200det_roi_heads_decode(const void* class_logits, const void* box_regressio
                           (float*)boxes_out, (float*)scores_out, valid, (cudaStream_t)stream);
 }
 
+int b200det_segmented_topk(const void* scores, int64_t B, int64_t A, const int32_t* level_ends,
+                           int num_levels, int64_t k, int64_t* out_idx, int64_t P, void* stream) {
+  if (!level_ends) return fail(B200DET_EINVAL, "segmented_topk: null level_ends");
+  return segmented_topk((const float*)scores, B, A, level_ends, num_levels, k, out_idx, P, (cudaStream_t)stream);
+}
+
 int b200det_relayout(const void* src, void* dst, int dtype, int64_t batch, int64_t rows, int64_t cols,
                      void* stream) {
   if (batch < 0 || rows < 0 || cols < 0) return fail(B200DET_EINVAL, "relayout: negative size");

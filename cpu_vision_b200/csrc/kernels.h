@@ -84,6 +84,9 @@ int clip_filter_boxes(const void* boxes, const void* scores, int dtype, long lon
                       const float* sizes, double min_size, double score_thresh, int strict, void* out,
                       uint8_t* valid, cudaStream_t st);
 
+// topk_sm100.cu: top-k per pyramid level of the [B, A] objectness, indices in descending score order (ties by index)
+int segmented_topk(const float* scores, long long B, long long A, const int32_t* level_ends, int num_levels,
+                   long long k, int64_t* out_idx, long long P, cudaStream_t st);
 // box_ops_sm100.cu: the RPN side between top-k and NMS in one pass (gather, sigmoid, level, clip, filters), fp32
 int rpn_select(const float* proposals, const float* objectness, const int64_t* top_idx, int B, long long A, int P,
                const float* sizes, const int* level_ends, int num_levels, double min_size, double score_thresh,

@@ -17,6 +17,7 @@ arithmetic are library element-wise ops, written in the reference's operation or
 No CPU fallback: CUDA tensors only.
 """
 import math
+import os
 from typing import List, Sequence, Tuple
 
 import torch
@@ -43,7 +44,13 @@ def _gather_kept(keep: Tensor, counts: Tensor, off: Sequence[int], *tensors: Ten
 
 
 def _get_top_n_idx(objectness: Tensor, num_anchors_per_level: Sequence[int], pre_nms_top_n: int) -> Tensor:
-    """rpn.py:231-240: top-k per level, indices into the concatenated anchors."""
+    """rpn.py:231-240: top-k per level, indices into the concatenated anchors.  fp32 logits, at most 8 levels and
+    k <= 2048: one launch for all images and levels (b200det_segmented_topk; equal scores in ascending index order,
+    which torch.topk leaves unspecified).  Anything else: the reference's loop over the levels."""
+    if (objectness.dtype == torch.float32 and objectness.is_cuda and 1 <= len(num_anchors_per_level) <= 8
+            and 1 <= pre_nms_top_n <= capi.SEGMENTED_TOPK_MAX_K and objectness.shape[0] <= 65535
+            and sum(num_anchors_per_level) == objectness.shape[1] and os.environ.get("B200DET_TOPK", "1") != "0"):
+        return capi.segmented_topk(objectness, num_anchors_per_level, pre_nms_top_n)
     r, offset = [], 0
     for ob in objectness.split(list(num_anchors_per_level), 1):
         num_anchors = ob.shape[1]

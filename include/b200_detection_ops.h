@@ -284,6 +284,19 @@ int b200det_rpn_select(
     const int32_t* level_ends, int num_levels, double min_size, double score_thresh,
     void* boxes_out, void* scores_out, int64_t* levels_out, uint8_t* valid, void* stream);
 
+/* Top-k per pyramid level of the RPN objectness, all images and levels in ONE launch.  Replaces
+ * RegionProposalNetwork._get_top_n_idx (torchvision/models/detection/rpn.py:231-240): the loop over levels of
+ * `ob.topk(min(pre_nms_top_n, num_anchors), dim=1)`, `+ offset` and `cat`.
+ *   scores      : device fp32 [B, A] (logits; NaN ranks first like torch.topk)
+ *   level_ends  : HOST int[num_levels <= 8], cumulative anchors per level, the last one == A
+ *   k           : 1 .. 2048 (B200DET_ENOSUP beyond: the caller keeps torch.topk)
+ *   out_idx     : device int64 [B, P], P = sum over levels of min(k, anchors of the level); per level the indices
+ *                 (into A) of its top-k scores in descending score order.  Equal scores come in ascending index
+ *                 order -- torch.topk leaves the order of ties unspecified. */
+int b200det_segmented_topk(
+    const void* scores, int64_t B, int64_t A, const int32_t* level_ends,
+    int num_levels, int64_t k, int64_t* out_idx, int64_t P, void* stream);
+
 /* The RoIHeads side before NMS in ONE pass (torchvision/models/detection/roi_heads.py:682-716 with
  * BoxCoder.decode, models/detection/_utils.py:162-224): softmax over the NC class logits, the box of every class
  * c >= 1 decoded from box_regression in the reference's operation order, clipped to the proposal's image, and
