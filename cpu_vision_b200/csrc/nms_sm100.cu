@@ -9,9 +9,12 @@
 //        cub::DeviceRadixSort::SortPairsDescending, nms_max_coord_kernel, nms_gather_kernel.
 //   4. nms_mask_kernel      upper-triangular 64x64 IoU>thr bit tiles
 //                           (replaces nms_kernel_impl, cuda/nms_kernel.cu:31-78)
+//   5b. nms_resolve_kernel  (sets of up to 13312 boxes) the greedy result by monotone propagation of finally kept /
+//                           finally removed boxes on all SMs, a CTA per 64-box column block; decides everything
+//                           in a few rounds unless suppression chains run deep across blocks
 //   5. nms_scan_smem_kernel / nms_scan_kernel   greedy keep scan on the device, one CTA
 //                           (replaces the D2H copy + host loop, :136-159);
-//                           writes keep[] = order[kept] and the count.
+//                           writes keep[] = order[kept] and the count.  Returns at once when 5b decided every box.
 // Segmented (per-image) variant: see "segmented NMS" below.
 //
 // IoU follows devIoU (cuda/nms_kernel.cu:16-29) with every operation an
