@@ -1,7 +1,7 @@
 // nms_sm100.cu -- greedy NMS and class-aware NMS, entirely on the device.
 //
 // Pipeline (all on the caller's stream, no host round trip):
-//   1-3. up to 8192 boxes: nms_front_rank_kernel -- every CTA stages all fp32 sort keys in shared memory and ranks
+//   1-3. up to 13312 boxes: nms_front_rank_kernel -- every CTA stages all fp32 sort keys in shared memory and ranks
 //        64 of them by counting (stable: ties keep ascending original index like scores.sort(stable=True,
 //        descending=True), cuda/nms_kernel.cu:112-113), reduces boxes.max() for the coordinate trick
 //        (boxes.py:91-93) and gathers its boxes into score order (B200DET_NMS_FRONT=block: the one-CTA block
@@ -276,6 +276,7 @@ __global__ void __launch_bounds__(kSortThreads) nms_front_small_kernel(
 // Keys are compared as cub compares floats (radix order: sign-flipped bit patterns, -0 ranks with +0), so ties,
 // NaN scores and signed zeros land where the block sort and the device-wide sort put them.
 constexpr int kRankKeys = 64, kRankSplit = 4, kRankThreads = kRankKeys * kRankSplit;
+constexpr int kRankMax = 13312;  // 52 KB of keys per CTA; the sets the shared-memory scan and the resolve kernel take
 
 __device__ __forceinline__ unsigned radix_order_key(float f) {
   unsigned b = __float_as_uint(f);
@@ -1153,20 +1154,29 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
   const int th = 256, bl = (int)((n + th - 1) / th);
   const int col_blocks = (int)((n + kTile - 1) / kTile);
   constexpr bool f64 = std::is_same<T, double>::value;
+  // one-launch front ends: the rank sort over all SMs for sets of up to kRankMax boxes, the one-CTA block radix sort
+  // (B200DET_NMS_FRONT=block, read per call) for up to kSortMax
+  const char* front = getenv("B200DET_NMS_FRONT");
+  const bool front_block = front && front[0] == 'b';
+  const long long front_max = front_block ? kSortMax : kRankMax;
   if (f64) {
     nms_prepare_kernel_f64<<<bl, th, 0, st>>>((const double*)scores, n, (double*)L.keys_in, L.idx_in);
     B200DET_CUDA_OK(cub::DeviceRadixSort::SortPairsDescending(
         L.cub_tmp, const_cast<size_t&>(L.cub_bytes), (const double*)L.keys_in, (double*)L.keys_out,
         (const int32_t*)L.idx_in, L.order, (int)n, 0, 64, st));
-  } else if (n <= kSortMax) {
+  } else if (n <= front_max) {
     if constexpr (!f64) {
-      const char* front = getenv("B200DET_NMS_FRONT");  // "block": the one-CTA block radix sort (read per call)
-      if (front && front[0] == 'b')
+      if (front_block) {
         nms_front_small_kernel<T><<<1, kSortThreads, 0, st>>>((const T*)boxes, (const T*)scores, idxs, (int)n, mode,
                                                               (Box4f*)L.sorted, mode == 2 ? L.cls : nullptr, L.order);
-      else
-        nms_front_rank_kernel<T><<<(int)((n + kRankKeys - 1) / kRankKeys), kRankThreads, (size_t)((n + 3) / 4) * 16, st>>>(
+      } else {
+        const size_t ksmem = (size_t)((n + 3) / 4) * 16;  // all n keys in every CTA's shared memory
+        if (ksmem > 48 * 1024)
+          B200DET_CUDA_OK(cudaFuncSetAttribute(nms_front_rank_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)((size_t)kRankMax * 4)));
+        nms_front_rank_kernel<T><<<(int)((n + kRankKeys - 1) / kRankKeys), kRankThreads, ksmem, st>>>(
             (const T*)boxes, (const T*)scores, idxs, (int)n, mode, (Box4f*)L.sorted, mode == 2 ? L.cls : nullptr, L.order);
+      }
     }
   } else {
     nms_prepare_kernel<T><<<bl, th, 0, st>>>((const T*)scores, n, (float*)L.keys_in, L.idx_in);
@@ -1174,7 +1184,7 @@ int nms_t(const void* boxes, const void* scores, const int64_t* idxs, long long 
         L.cub_tmp, const_cast<size_t&>(L.cub_bytes), (const float*)L.keys_in, (float*)L.keys_out,
         (const int32_t*)L.idx_in, L.order, (int)n, 0, 32, st));
   }
-  if (f64 || n > kSortMax) {
+  if (f64 || n > front_max) {
     if (mode == 1)
       nms_max_coord_kernel<T><<<1, 1024, 0, st>>>((const T*)boxes, n * 4, (A*)L.maxc);
     nms_gather_kernel<T><<<bl, th, 0, st>>>((const T*)boxes, idxs, L.order, n, mode, (const A*)L.maxc,

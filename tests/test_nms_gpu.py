@@ -373,7 +373,7 @@ def test_iou_on_the_threshold_and_degenerate_boxes(capi):
         assert torch.equal(got.cpu(), oracle.batched_nms(grid[:600], s[:600], idx, 0.5, name)), name
 
 
-@pytest.mark.parametrize("n", [7, 4096, 8191, 8192, 8193])
+@pytest.mark.parametrize("n", [7, 4096, 8191, 8192, 8193, 13312, 13313])
 def test_sort_front_ends_agree_with_the_oracle_on_special_scores(capi, n):
     """Sets of up to 8192 boxes take the single-CTA sort, larger ones the device-wide radix sort: signed zeros,
     infinities, long tie runs and 16-bit scores must rank the same way in both, i.e. like the oracle's stable
@@ -396,7 +396,7 @@ def test_sort_front_ends_agree_with_the_oracle_on_special_scores(capi, n):
     assert torch.equal(capi.nms(bh.to(DEV), sh.to(DEV), 0.5).cpu(), oracle.nms(bh.float(), sh.float(), 0.5))
 
 
-@pytest.mark.parametrize("n", [1, 3, 64, 65, 257, 5000, 8192])
+@pytest.mark.parametrize("n", [1, 3, 64, 65, 257, 5000, 8192, 10000, 13312])
 def test_front_ends_rank_sort_and_block_sort(capi, n, monkeypatch):
     """The rank sort over all SMs (default for sets of up to 8192 boxes) and the one-CTA block radix sort
     (B200DET_NMS_FRONT=block, read per call) must give the same keep list, which is the oracle's: tie runs,
