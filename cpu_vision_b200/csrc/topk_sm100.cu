@@ -45,6 +45,7 @@ __global__ void __launch_bounds__(kTopkThreads) segmented_topk_kernel(const floa
   using Scan = cub::BlockScan<int, kTopkThreads>;
   using Sort = cub::BlockRadixSort<unsigned long long, kTopkThreads, kTopkItems>;
   using SortS = cub::BlockRadixSort<unsigned, kTopkThreads, kTopkItems>;
+  using SortP = cub::BlockRadixSort<unsigned, kTopkThreads, kTopkItems, unsigned>;
   __shared__ union {  // the phases never overlap in time
     typename SortS::TempStorage sample;    // (0) sort of the sample
     struct {
@@ -52,7 +53,8 @@ __global__ void __launch_bounds__(kTopkThreads) segmented_topk_kernel(const floa
       typename Scan::TempStorage scan;
     } sel;                                 // (1) radix select
     unsigned long long buf[kTopkMax];      // (2) collected (key, ~index) composites
-    typename Sort::TempStorage sort;       // (3) block radix sort
+    typename SortP::TempStorage sortp;     // (3) block radix sort of (key, index) pairs
+    typename Sort::TempStorage sort;       // (3') of 64-bit composites when equal keys came out of index order
   } tmp;
   unsigned long long* buf = tmp.buf;
   __shared__ unsigned s_prefix, s_need, s_floor;
@@ -77,13 +79,13 @@ __global__ void __launch_bounds__(kTopkThreads) segmented_topk_kernel(const floa
 #pragma unroll
       for (int q = 0; q < kTopkItems; ++q)
         smp[q] = topk_key(__ldg(s + (long long)(tid * kTopkItems + q) * n / kTopkMax));
-      SortS(tmp.sample).SortDescending(smp);
+      SortS(tmp.sample).SortDescending(smp, 16, 32);  // by the upper 16 bits: 4 passes instead of 8
       const float m = (float)kTopkMax * (float)kk / (float)n;
       const int r = (int)(m + 4.f * sqrtf(m) + 8.f);
       if (r < kTopkMax) {
 #pragma unroll
         for (int q = 0; q < kTopkItems; ++q)
-          if (tid * kTopkItems + q == r) s_floor = smp[q];
+          if (tid * kTopkItems + q == r) s_floor = smp[q] & 0xffff0000u;  // (a lower bound of the sample's r-th key)
       } else if (tid == 0) {
         s_floor = 0u;
       }
@@ -185,20 +187,44 @@ __global__ void __launch_bounds__(kTopkThreads) segmented_topk_kernel(const floa
     }
   }
   __syncthreads();
-  // s_cnt == kk.  Descending (key, then ascending index): descending on the composite.
+  // s_cnt == kk.  Descending keys, equal keys by ascending index.  The pairs are sorted by key alone (8 passes of
+  // a stable 32-bit sort instead of 16 of a 64-bit one); equal keys keep the order they were collected in, which is
+  // arbitrary -- ties among the top k are rare, so they are looked for afterwards and only a block that finds a
+  // run out of index order sorts the 64-bit (key, ~index) composites.
   unsigned long long items[kTopkItems];
+  unsigned keys[kTopkItems], vals[kTopkItems];
 #pragma unroll
   for (int q = 0; q < kTopkItems; ++q) {
     const int j = tid * kTopkItems + q;
-    items[q] = j < kk ? buf[j] : 0ULL;
+    items[q] = j < kk ? buf[j] : 0ULL;   // (0 is below every real key)
+    keys[q] = (unsigned)(items[q] >> 32);
+    vals[q] = 0xffffffffu - (unsigned)(items[q] & 0xffffffffULL);
   }
   __syncthreads();
-  Sort(tmp.sort).SortDescending(items);
+  SortP(tmp.sortp).SortDescending(keys, vals);
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < kTopkItems; ++q) buf[tid * kTopkItems + q] = ((unsigned long long)keys[q] << 32) | vals[q];
+  __syncthreads();
+  bool bad = false;
+#pragma unroll
+  for (int q = 0; q < kTopkItems; ++q) {
+    const int j = tid * kTopkItems + q;
+    if (j + 1 < kk) {
+      const unsigned long long nx = buf[j + 1];
+      bad |= (unsigned)(nx >> 32) == keys[q] && (unsigned)(nx & 0xffffffffULL) < vals[q];
+    }
+  }
+  if (__syncthreads_or(bad)) {
+    Sort(tmp.sort).SortDescending(items);
+#pragma unroll
+    for (int q = 0; q < kTopkItems; ++q) vals[q] = 0xffffffffu - (unsigned)(items[q] & 0xffffffffULL);
+  }
   int64_t* o = out_idx + b * P + lv.out_off[l];
 #pragma unroll
   for (int q = 0; q < kTopkItems; ++q) {
     const int j = tid * kTopkItems + q;
-    if (j < kk) o[j] = (int64_t)lo + (int64_t)(0xffffffffu - (unsigned)(items[q] & 0xffffffffULL));
+    if (j < kk) o[j] = (int64_t)lo + (int64_t)vals[q];
   }
 }
 
