@@ -102,6 +102,8 @@ class PushGather:
 
         self.capi, self.group, self.device = capi, group, torch.device(device)
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > 8:
+            raise ValueError("PushGather: at most 8 ranks (one NVLink domain; the kernel pushes to 7 peers)")
         es = torch.empty(0, dtype=dtype).element_size()
         self.slice_bytes = k_local * channels * pooled_h * pooled_w * es
         nbytes = max(self.world * self.slice_bytes, 16)
