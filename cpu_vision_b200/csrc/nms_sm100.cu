@@ -912,7 +912,8 @@ __global__ void __launch_bounds__(kResolveThreads) nms_resolve_kernel(
   const int nent = (j + 1) * kTile;
   for (int e = tid; e < nent; e += kResolveThreads) {
     const int b = e >> 6, r = e & 63;
-    u64 w = __ldcg(mask + tri_base(b, cb) + (long long)r * (cb - b) + (j - b));
+    // (the last block only has n - 64 b rows: nothing was written, and nothing is allocated, for the others)
+    u64 w = r < n - b * kTile ? __ldcg(mask + tri_base(b, cb) + (long long)r * (cb - b) + (j - b)) : 0ULL;
     if (b == j) w &= ~((2ULL << r) - 1ULL);  // diagonal word: bits right of the row only (row 63: none)
     col[e] = w;
   }
