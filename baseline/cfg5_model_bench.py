@@ -95,6 +95,14 @@ with torch.no_grad():
     a, b = stock_pp(), ours_pp()
     res["detections"] = sum(x.shape[0] for x in a[0])
     res["detections_batched"] = sum(x.shape[0] for x in b[0])
+# the whole model once more with the reference's classes routed through the mirrors (cpu_vision_b200.dropin)
+from cpu_vision_b200 import dropin  # noqa: E402
+
+with torch.no_grad():
+    dropin.enable()
+    res["whole_model_dropin_enabled_ms"] = timed(lambda: model(imgs), iters=3)
+    dropin.disable()
+res["images_per_s_whole_model_dropin_enabled"] = B / (res["whole_model_dropin_enabled_ms"] / 1e3)
 res["post_backbone_stock_ms"] = (res["filter_proposals_stock_loop_ms"] + res["box_roi_pool_ms"] +
                                  res["box_head_predictor_ms"] + res["postprocess_detections_stock_loop_ms"])
 res["post_backbone_batched_ms"] = (res["filter_proposals_batched_ms"] + res["box_roi_pool_fused_ms"] +

@@ -4,6 +4,7 @@ operator API of kaisun24/CPU-Vision (a torchvision 0.20 fork).
 Public surface (same names and signatures as the reference's torchvision.ops):
     roi_align, RoIAlign, MultiScaleRoIAlign, nms, batched_nms, roi_pool, RoIPool, ps_roi_pool, PSRoIPool, ps_roi_align, PSRoIAlign
     cpu_vision_b200.detection    filter_proposals / postprocess_detections batched over images
+    cpu_vision_b200.dropin       enable() / disable(): the reference's detection classes on the mirrors, at run time
 Lower level:
     cpu_vision_b200.capi         ctypes binding of the C-ABI (include/b200_detection_ops.h)
     cpu_vision_b200.sharding     shard-by-image multi-GPU harness (NCCL all-gather)

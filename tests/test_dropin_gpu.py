@@ -151,3 +151,52 @@ def test_fasterrcnn_resnet50_fpn_cuda_vs_cpu():
     must run through."""
     assert "model ok" in _run(["-c", MODEL.replace("B)", "2)").replace("CHECK", "True")])
     assert "model ok" in _run(["-c", MODEL.replace("B)", "64)").replace("CHECK", "False")])
+
+
+ENABLE = r'''
+import torch, torchvision
+import cpu_vision_b200
+from cpu_vision_b200 import dropin
+from torchvision.models.detection import fasterrcnn_resnet50_fpn
+torch.manual_seed(0)
+m = fasterrcnn_resnet50_fpn(weights=None, weights_backbone=None, num_classes=91, rpn_pre_nms_top_n_test=2000,
+                            rpn_post_nms_top_n_test=2000, box_score_thresh=0.0).eval().cuda()
+imgs = [torch.rand(3, 800, 1088, device="cuda") for _ in range(4)]
+seen = {}
+def hook(name):
+    def f(mod, inp, out):
+        seen.setdefault(name, []).append(out)
+    return f
+m.rpn.register_forward_hook(hook("rpn"))
+m.roi_heads.box_roi_pool.register_forward_hook(hook("pool"))
+with torch.no_grad():
+    ref = m(imgs)
+    names = dropin.enable()
+    assert names == ["RegionProposalNetwork.filter_proposals", "RoIHeads.postprocess_detections",
+                     "ops.poolers._multiscale_roi_align"], names
+    got = m(imgs)
+    dropin.disable()
+    again = m(imgs)
+torch.cuda.synchronize()
+# the RPN's proposals and the pooled box features: bit for bit (same kernels underneath, fused launches)
+for a, b in zip(seen["rpn"][0][0], seen["rpn"][1][0]):
+    assert torch.equal(a, b)
+assert torch.equal(seen["pool"][0], seen["pool"][1])
+# the detections: same count and labels; boxes to 1e-3 px, scores to 1e-6 (the softmax sum rounds differently)
+for r, g, a in zip(ref, got, again):
+    assert torch.equal(r["boxes"], a["boxes"]) and torch.equal(r["scores"], a["scores"])   # disable() restored the loops
+    assert len(r["boxes"]) == len(g["boxes"]) > 0
+    kr = torch.argsort(r["labels"] * 1e6 + r["boxes"][:, 0] + r["boxes"][:, 1] * 1e-3)
+    kg = torch.argsort(g["labels"] * 1e6 + g["boxes"][:, 0] + g["boxes"][:, 1] * 1e-3)
+    assert torch.equal(r["labels"][kr], g["labels"][kg])
+    torch.testing.assert_close(g["boxes"][kg], r["boxes"][kr], rtol=0, atol=1e-3)
+    torch.testing.assert_close(g["scores"][kg], r["scores"][kr], rtol=0, atol=1e-6)
+print("enable ok", sum(len(o["boxes"]) for o in got))
+'''
+
+
+@needs_ref
+def test_enable_dropin_gives_the_same_detections():
+    """cpu_vision_b200.dropin.enable(): the reference's RegionProposalNetwork / RoIHeads / MultiScaleRoIAlign run the
+    batched and fused mirrors; proposals and pooled features bit for bit, detections within the softmax rounding."""
+    assert "enable ok" in _run(["-c", ENABLE])
