@@ -103,3 +103,47 @@ def test_gloo_world2_gather():
     for p in procs:
         p.join(60)
     assert res == [(0, True), (1, True)]
+
+
+def test_dropin_enable_patches_and_falls_through_on_cpu():
+    """cpu_vision_b200.dropin under the reference's package (baseline/_ref, a process of its own): enable() replaces
+    the three entry points, CPU tensors fall through to the reference's own code (no CPU fallback of ours exists),
+    disable() puts the reference's functions back."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref = os.path.join(root, "baseline", "_ref")
+    if not os.path.exists(os.path.join(ref, "torchvision", "_C.so")):
+        import pytest
+
+        pytest.skip("baseline/_ref not built (python baseline/build_ref.py)")
+    code = r'''
+import torch, torchvision
+import cpu_vision_b200
+from cpu_vision_b200 import dropin
+from torchvision.models.detection import rpn, roi_heads
+from torchvision.ops import poolers, MultiScaleRoIAlign
+assert "_ref" in torchvision.__file__
+orig = (rpn.RegionProposalNetwork.filter_proposals, roi_heads.RoIHeads.postprocess_detections, poolers._multiscale_roi_align)
+torch.manual_seed(0)
+feats = {"0": torch.randn(2, 8, 32, 32), "1": torch.randn(2, 8, 16, 16)}
+boxes = [torch.tensor([[4.0, 4.0, 60.0, 50.0], [10.0, 20.0, 120.0, 100.0]]), torch.tensor([[0.0, 0.0, 30.0, 30.0]])]
+pool = MultiScaleRoIAlign(["0", "1"], 3, 2)
+want = pool(feats, boxes, [(128, 128), (128, 128)])
+names = dropin.enable()
+assert len(names) == 3 and dropin.enable() == names                      # idempotent
+now = (rpn.RegionProposalNetwork.filter_proposals, roi_heads.RoIHeads.postprocess_detections, poolers._multiscale_roi_align)
+assert all(a is not b for a, b in zip(orig, now))
+got = pool(feats, boxes, [(128, 128), (128, 128)])                        # CPU tensors: the reference's own loop
+assert torch.equal(got, want)
+dropin.disable()
+back = (rpn.RegionProposalNetwork.filter_proposals, roi_heads.RoIHeads.postprocess_detections, poolers._multiscale_roi_align)
+assert all(a is b for a, b in zip(orig, back))
+print("dropin cpu ok")
+'''
+    env = dict(os.environ)
+    env["PYTHONPATH"] = os.pathsep.join([ref, root, env.get("PYTHONPATH", "")])
+    p = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0 and "dropin cpu ok" in p.stdout, (p.stdout[-2000:], p.stderr[-2000:])
