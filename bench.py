@@ -227,6 +227,17 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def port_evidence(key):
+    """The SM -> L2 request port of the backward in the committed ncu capture of `key` (profiles/traffic.json): the unit
+    that bounds the scatter; None when there is no capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f).get(key, {})
+        return {"bwd": t.get("bwd_sm_l2_port"), "dram_bytes_bwd": t.get("bwd"), "source": t.get("source")}
+    except Exception:
+        return None
+
+
 def workload_config(name):
     return {
         "workload": f"{name}: MultiScaleRoIAlign fwd+bwd, 4 FPN levels of 800x1088 (200x272..25x34), C=256, "
@@ -491,7 +502,8 @@ def secondary_legs(capi, dev, peak):
     res["cfg1_roi_align_fp32"] = {
         "fwd_ms": f_ms, "bwd_ms": b_ms, "fwd_rois_per_s": 2000 / (f_ms / 1e3),
         "fwd_bwd_rois_per_s": 2000 / ((f_ms + b_ms) / 1e3), "fwd_frac_of_hbm": fb / (f_ms / 1e3) / 1e9 / peak,
-        "bwd_frac_of_hbm": fb / (b_ms / 1e3) / 1e9 / peak, "l2": "flushed between iterations"}
+        "bwd_frac_of_hbm": fb / (b_ms / 1e3) / 1e9 / peak, "l2": "flushed between iterations",
+        "sm_l2_port": port_evidence("cfg1")}
     del x, g, gi
     # cfg2: batched_nms 5000 boxes x 80 classes, IoU 0.5 (coordinate-trick branch on CUDA, boxes.py:72)
     n = 5000
@@ -699,7 +711,8 @@ def cfg4_leg(capi, dev, rank, world, dist, peak):
         "images": B, "rois": B * per_img, "images_per_rank": nb, "scaling": "strong", "fwd_ms": f_ms, "bwd_ms": b_ms,
         "bwd_rois_per_s": B * per_img / (b_ms / 1e3), "fwd_bwd_rois_per_s": B * per_img / ((f_ms + b_ms) / 1e3),
         "bwd_frac_of_hbm": (fb + ob + K * 20) / (b_ms / 1e3) / 1e9 / peak,
-        "fwd_frac_of_hbm": (fb + ob + K * 20) / (f_ms / 1e3) / 1e9 / peak}}
+        "fwd_frac_of_hbm": (fb + ob + K * 20) / (f_ms / 1e3) / 1e9 / peak,
+        "sm_l2_port_16_image_slice": port_evidence("cfg4_slice")}}
     if world == 1:
         return res
     # --- the exchange
