@@ -94,6 +94,36 @@ __global__ void k_bulk(const char* __restrict__ p, size_t bytes, int chunk, int 
   }
 }
 
+
+// TMA bulk store / bulk reduce-add (fp32) from shared memory: does the SM -> L2 port move more bytes per cycle with
+// bulk requests than with st.128 / red.v4.f32 (round 2: that port bounds the scatter backward)?
+// One thread per CTA issues cp.async.bulk / cp.reduce.async.bulk of `chunk` bytes, `depth` groups in flight.
+template <bool RED>
+__global__ void k_bulk_out(char* __restrict__ p, size_t bytes, int chunk, int depth, int reps) {
+  extern __shared__ __align__(128) char sm[];
+  for (int i = threadIdx.x; i < chunk / 4; i += blockDim.x) reinterpret_cast<float*>(sm)[i] = RED ? 1.0f : 0.0f;
+  __syncthreads();
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (threadIdx.x != 0) return;
+  const unsigned sbase = (unsigned)__cvta_generic_to_shared(sm);
+  const size_t nchunks = bytes / chunk;
+  int inflight = 0;
+  for (int r = 0; r < reps; ++r)
+    for (size_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+      char* g = p + c * (size_t)chunk;
+      if (RED)
+        asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+                     ::"l"(g), "r"(sbase), "r"(chunk) : "memory");
+      else
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g), "r"(sbase), "r"(chunk) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      if (++inflight >= depth) {
+        asm volatile("cp.async.bulk.wait_group.read 7;" ::: "memory");
+      }
+    }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 template <typename F>
 float timeit(F f, int iters) {
   cudaEvent_t a, b;
@@ -150,6 +180,14 @@ int main() {
         float ms = timeit([&] { k_bulk<<<grid, 32, smem>>>(buf, bytes, chunk, stages, reps); }, 3);
         printf("%s bulk %5d B x%d stages, %d CTA/SM: %8.1f GB/s\n", tag, chunk, stages, per_sm,
                bytes * (double)reps / ms / 1e6);
+      }
+    for (int chunk = 1024; chunk <= 16384; chunk *= 4)
+      for (int per_sm = 4; per_sm <= 16; per_sm *= 2) {
+        const int grid = sms * per_sm;
+        float ms = timeit([&] { k_bulk_out<false><<<grid, 128, chunk>>>(buf, bytes, chunk, 8, reps); }, 3);
+        printf("%s bulk STORE  %5d B, %2d CTA/SM: %8.1f GB/s\n", tag, chunk, per_sm, bytes * (double)reps / ms / 1e6);
+        ms = timeit([&] { k_bulk_out<true><<<grid, 128, chunk>>>(buf, bytes, chunk, 8, reps); }, 3);
+        printf("%s bulk RED.f32 %5d B, %2d CTA/SM: %8.1f GB/s\n", tag, chunk, per_sm, bytes * (double)reps / ms / 1e6);
       }
   }
   cudaMemset(buf, 0, 1024);
