@@ -44,6 +44,20 @@ def test_argument_errors_without_gpu():
     assert l.b200det_batched_nms(None, None, None, 0, 4, 0.5, 5, None, ctypes.c_void_p(8), None, 0, None) == -1
     assert l.b200det_nms_workspace_bytes(5000) > 5000 * 79 * 8
     assert l.b200det_nms_workspace_bytes(0) > 0
+    # the round-2 entry points: the push forward refuses more than 7 peers and null peer arrays, the per-level top-k
+    # refuses k beyond 2048 (ENOSUP: the caller keeps torch.topk), level ends that do not end at A, a wrong P
+    le = (ctypes.c_int32 * 2)(100, 300)
+    assert l.b200det_msroi_align_forward_push(None, None, None, None, 1, 1, None, None, 0, None, None, 8, 1, 0, 1, 256,
+                                              4, 7, 7, 2, 0, 2, 5, 224, 4, 1e-6, None) == -1
+    assert b"at most 7 peer outputs" in l.b200det_last_error()
+    assert l.b200det_msroi_align_forward_push(None, None, None, None, 1, 1, None, None, 0, None, None, 2, 1, 0, 1, 256,
+                                              4, 7, 7, 2, 0, 2, 5, 224, 4, 1e-6, None) == -1
+    assert l.b200det_segmented_topk(None, 2, 300, le, 2, 4096, None, 400, None) == -2
+    assert l.b200det_segmented_topk(None, 2, 301, le, 2, 100, None, 200, None) == -1
+    assert l.b200det_segmented_topk(None, 2, 300, le, 2, 150, None, 999, None) == -1
+    assert b"P must be" in l.b200det_last_error()
+    assert l.b200det_segmented_topk(None, 0, 300, le, 2, 150, None, 250, None) == 0      # no images: nothing to do
+    assert l.b200det_peer_alloc(0, None) == -1 and l.b200det_peer_export(None, None) == -1
 
 
 def test_dispatcher_registration():
